@@ -1,0 +1,164 @@
+// arith.cuh — element-wise, block and matrix-product kernels over [poly][limb][coeff].
+//
+// Replaces cuda/src/matrix/MatrixArith.cu: block_elementwise_all_limbs_kernel (:26),
+// block_add_rect_all_limbs_kernel (:137), block_matmul_kernel (:191, one launch per
+// limb, stride-bytes_per_poly loads, `__int128 %` per product and per add) and
+// block_equal_kernel (:602).  Here every access is a 128-bit vector along the
+// coefficient axis, all limbs go in one launch, and products are accumulated lazily
+// with one Barrett reduction per `fold` terms.
+#pragma once
+#include "modarith.cuh"
+
+namespace gp {
+
+template <typename T, int V> struct alignas(sizeof(T) * V) Vec { T v[V]; };
+template <typename T, int V> __device__ __forceinline__ Vec<T, V> ldv(const T *p) {
+    return *reinterpret_cast<const Vec<T, V> *>(p);
+}
+template <typename T, int V> __device__ __forceinline__ void stv(T *p, const Vec<T, V> &x) {
+    *reinterpret_cast<Vec<T, V> *>(p) = x;
+}
+
+enum class EwOp { Add, Sub, MulScalar };
+
+// out[p] = a[p] (+|-) b[p], or a[p] * s (s one poly).  total = words / V.
+template <typename T, int V, EwOp OP>
+__global__ void elementwise_kernel(T *__restrict__ out, const T *__restrict__ a, const T *__restrict__ b, size_t total,
+                                   uint32_t limbs, uint32_t logn, const LimbConst<T> *__restrict__ lc) {
+    const size_t step = (size_t)gridDim.x * blockDim.x;
+    const size_t poly_words = (size_t)limbs << logn;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
+        const size_t off = i * V;
+        const uint32_t limb = (uint32_t)((off >> logn) % limbs);
+        const LimbConst<T> c = lc[limb];
+        Vec<T, V> x = ldv<T, V>(a + off), y, r;
+        if (OP == EwOp::MulScalar)
+            y = ldv<T, V>(b + (off % poly_words));
+        else
+            y = ldv<T, V>(b + off);
+#pragma unroll
+        for (int k = 0; k < V; k++) {
+            if (OP == EwOp::Add) r.v[k] = add_mod<T>(x.v[k], y.v[k], c.q);
+            if (OP == EwOp::Sub) r.v[k] = sub_mod<T>(x.v[k], y.v[k], c.q);
+            if (OP == EwOp::MulScalar) r.v[k] = mul_mod<T>(x.v[k], y.v[k], c);
+        }
+        stv<T, V>(out + off, r);
+    }
+}
+
+struct RectGeom {
+    size_t dst_cols, src_cols, dst_row, dst_col, src_row, src_col, rows, cols;
+};
+// dst block += src block (mod q); total = rows*cols*poly_words / V
+template <typename T, int V>
+__global__ void add_rect_kernel(T *__restrict__ dst, const T *__restrict__ src, RectGeom g, size_t total, uint32_t limbs,
+                                uint32_t logn, const LimbConst<T> *__restrict__ lc) {
+    const size_t step = (size_t)gridDim.x * blockDim.x;
+    const size_t poly_words = (size_t)limbs << logn;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
+        const size_t off = i * V, rp = off / poly_words, w = off % poly_words;
+        const size_t r = rp / g.cols, cc = rp % g.cols;
+        const uint32_t limb = (uint32_t)(w >> logn);
+        const T q = lc[limb].q;
+        T *d = dst + ((g.dst_row + r) * g.dst_cols + g.dst_col + cc) * poly_words + w;
+        const T *s = src + ((g.src_row + r) * g.src_cols + g.src_col + cc) * poly_words + w;
+        Vec<T, V> x = ldv<T, V>(d), y = ldv<T, V>(s);
+#pragma unroll
+        for (int k = 0; k < V; k++) x.v[k] = add_mod<T>(x.v[k], y.v[k], q);
+        stv<T, V>(d, x);
+    }
+}
+
+template <typename T, int V>
+__global__ void equal_kernel(const T *__restrict__ a, const T *__restrict__ b, size_t total, int *__restrict__ diff) {
+    const size_t step = (size_t)gridDim.x * blockDim.x;
+    bool d = false;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
+        Vec<T, V> x = ldv<T, V>(a + i * V), y = ldv<T, V>(b + i * V);
+#pragma unroll
+        for (int k = 0; k < V; k++) d |= x.v[k] != y.v[k];
+    }
+    if (__any_sync(0xffffffffu, d) && (threadIdx.x & 31) == 0) atomicOr(diff, 1);
+}
+
+// scalar fill of whole polys: out[poly][limb][*] = vals[poly*limbs + limb] (gadget matrix in EVAL form:
+// a constant polynomial evaluates to the constant at every slot).
+template <typename T>
+__global__ void fill_const_polys_kernel(T *__restrict__ out, const T *__restrict__ vals, size_t total_words, uint32_t logn) {
+    const size_t step = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total_words; i += step) out[i] = vals[i >> logn];
+}
+
+// ---- matrix product ----------------------------------------------------------------
+// out(r x c) = A(r x k) * B(k x c), independently per (limb, slot).  A thread owns a
+// TR x TC tile of output polynomials at V consecutive slots of one limb.
+// grid: x = limbs * ceil(n / (V*blockDim.x)), y = ceil(c/TC), z = ceil(r/TR).
+// The product lands in columns [out_col0, out_col0 + cols) of an output with out_cols columns.
+template <typename T, int V, int TR, int TC>
+__global__ void __launch_bounds__(128)
+matmul_kernel(T *__restrict__ out, const T *__restrict__ A, const T *__restrict__ B, uint32_t rows, uint32_t inner,
+              uint32_t cols, uint32_t out_cols, uint32_t out_col0, uint32_t limbs, uint32_t logn, uint32_t fold,
+              const LimbConst<T> *__restrict__ lc) {
+    const uint32_t chunks = ((1u << logn) / V + blockDim.x - 1) / blockDim.x;
+    const uint32_t limb = blockIdx.x / chunks, chunk = blockIdx.x % chunks;
+    const uint32_t slot = (chunk * blockDim.x + threadIdx.x) * V;
+    if (slot >= (1u << logn)) return;
+    const size_t poly_words = (size_t)limbs << logn;
+    const size_t in_poly = ((size_t)limb << logn) + slot;
+    const uint32_t r0 = blockIdx.z * TR, c0 = blockIdx.y * TC;
+    const LimbConst<T> c = lc[limb];
+
+    Acc<T> acc[TR][TC][V];
+#pragma unroll
+    for (int i = 0; i < TR; i++)
+#pragma unroll
+        for (int j = 0; j < TC; j++)
+#pragma unroll
+            for (int v = 0; v < V; v++) acc[i][j][v].clear();
+
+    // clamp out-of-range tile members onto valid polynomials; their results are not stored
+    size_t arow[TR], bcol[TC];
+#pragma unroll
+    for (int i = 0; i < TR; i++) arow[i] = (size_t)min(r0 + i, rows - 1) * inner * poly_words + in_poly;
+#pragma unroll
+    for (int j = 0; j < TC; j++) bcol[j] = (size_t)min(c0 + j, cols - 1) * poly_words + in_poly;
+    const size_t bstep = (size_t)cols * poly_words;
+
+    uint32_t since = 0;
+#pragma unroll 2
+    for (uint32_t k = 0; k < inner; k++) {
+        Vec<T, V> a[TR], b[TC];
+#pragma unroll
+        for (int i = 0; i < TR; i++) a[i] = ldv<T, V>(A + arow[i] + (size_t)k * poly_words);
+#pragma unroll
+        for (int j = 0; j < TC; j++) b[j] = ldv<T, V>(B + bcol[j] + (size_t)k * bstep);
+#pragma unroll
+        for (int i = 0; i < TR; i++)
+#pragma unroll
+            for (int j = 0; j < TC; j++)
+#pragma unroll
+                for (int v = 0; v < V; v++) acc[i][j][v].mac(a[i].v[v], b[j].v[v]);
+        if (++since == fold) {
+            since = 0;
+#pragma unroll
+            for (int i = 0; i < TR; i++)
+#pragma unroll
+                for (int j = 0; j < TC; j++)
+#pragma unroll
+                    for (int v = 0; v < V; v++) acc[i][j][v].fold(c);
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < TR; i++)
+#pragma unroll
+        for (int j = 0; j < TC; j++) {
+            if (r0 + i < rows && c0 + j < cols) {
+                Vec<T, V> o;
+#pragma unroll
+                for (int v = 0; v < V; v++) o.v[v] = acc[i][j][v].result(c);
+                stv<T, V>(out + ((size_t)(r0 + i) * out_cols + out_col0 + c0 + j) * poly_words + in_poly, o);
+            }
+        }
+}
+
+}  // namespace gp

@@ -1,0 +1,92 @@
+// modarith.cuh — word-level modular arithmetic for the two device storage widths.
+//
+// Storage width T is chosen per context: uint32_t when every modulus is < 2^30,
+// uint64_t otherwise (moduli < 2^62).  The bounds leave room for Harvey-style lazy
+// butterflies that keep values in [0, 4q).
+//
+// Replaces the reference's `(unsigned __int128)a*b % mod` per product
+// (cuda/src/matrix/MatrixUtils.cu:541-545) with Shoup multiplication for known
+// twiddles and one Barrett reduction per lazily accumulated sum.
+#pragma once
+#include <stdint.h>
+#include <cuda_runtime.h>
+
+namespace gp {
+
+template <typename T> struct TwPair;
+template <> struct __align__(8) TwPair<uint32_t> { uint32_t w, ws; };
+template <> struct __align__(16) TwPair<uint64_t> { uint64_t w, ws; };
+
+// Per-limb constants, one entry per CRT limb, resident in global memory.
+template <typename T> struct LimbConst {
+    T q;             // modulus
+    T q2;            // 2q
+    T ninv, ninv_s;  // n^-1 mod q and its Shoup companion
+    T nw, nw_s;      // n^-1 * psi^-bitrev(1): merged last inverse-stage twiddle
+    T r64, r64_s;    // 2^64 mod q (+ Shoup), folds the high word of a 128-bit sum
+    uint64_t mu64;   // floor(2^64 / q): Barrett constant for 64-bit inputs
+    uint32_t bits;   // bit width of q
+    uint32_t pad;
+};
+
+__device__ __forceinline__ uint32_t mulhi(uint32_t a, uint32_t b) { return __umulhi(a, b); }
+__device__ __forceinline__ uint64_t mulhi(uint64_t a, uint64_t b) { return __umul64hi(a, b); }
+
+// a*w mod q in [0, 2q) for ANY word a, w < q, ws = floor(w * 2^wordbits / q).
+template <typename T> __device__ __forceinline__ T mul_shoup_lazy(T a, T w, T ws, T q) {
+    T h = mulhi(a, ws);
+    return a * w - h * q;
+}
+template <typename T> __device__ __forceinline__ T csub(T a, T q) { return a >= q ? a - q : a; }
+
+// x mod q for a 64-bit x (both widths use the 64-bit Barrett constant).
+template <typename T> __device__ __forceinline__ T red64(uint64_t x, const LimbConst<T> &c) {
+    uint64_t qh = __umul64hi(x, c.mu64);
+    uint64_t r = x - qh * (uint64_t)c.q;  // in [0, 2q)
+    return (T)(r >= (uint64_t)c.q ? r - c.q : r);
+}
+// (hi*2^64 + lo) mod q, u64 limbs.
+__device__ __forceinline__ uint64_t red128(uint64_t hi, uint64_t lo, const LimbConst<uint64_t> &c) {
+    uint64_t h = red64<uint64_t>(hi, c);
+    uint64_t a = mul_shoup_lazy<uint64_t>(h, c.r64, c.r64_s, c.q);  // [0,2q)
+    uint64_t b = red64<uint64_t>(lo, c);                             // [0,q)
+    uint64_t s = a + b;                                              // < 3q < 2^64
+    s = csub(s, c.q2);
+    return csub(s, c.q);
+}
+
+// Lazy accumulator for sum_k a_k*b_k mod q.
+template <typename T> struct Acc;
+template <> struct Acc<uint32_t> {
+    uint64_t v;
+    __device__ __forceinline__ void clear() { v = 0; }
+    __device__ __forceinline__ void mac(uint32_t a, uint32_t b) { v += (uint64_t)a * b; }
+    // products < 2^60: 16 terms fit 64 bits for q < 2^30
+    static constexpr int kTermsPerFold = 16;
+    __device__ __forceinline__ void fold(const LimbConst<uint32_t> &c) { v = red64<uint32_t>(v, c); }
+    __device__ __forceinline__ uint32_t result(const LimbConst<uint32_t> &c) const { return red64<uint32_t>(v, c); }
+};
+template <> struct Acc<uint64_t> {
+    uint64_t lo, hi;
+    __device__ __forceinline__ void clear() { lo = 0; hi = 0; }
+    __device__ __forceinline__ void mac(uint64_t a, uint64_t b) {
+        uint64_t pl = a * b, ph = __umul64hi(a, b);
+        lo += pl;
+        hi += ph + (lo < pl);
+    }
+    // products < 2^124: 16 terms fit 128 bits for q < 2^62
+    static constexpr int kTermsPerFold = 16;
+    __device__ __forceinline__ void fold(const LimbConst<uint64_t> &c) { lo = red128(hi, lo, c); hi = 0; }
+    __device__ __forceinline__ uint64_t result(const LimbConst<uint64_t> &c) const { return red128(hi, lo, c); }
+};
+
+template <typename T> __device__ __forceinline__ T mul_mod(T a, T b, const LimbConst<T> &c) {
+    Acc<T> acc;
+    acc.clear();
+    acc.mac(a, b);
+    return acc.result(c);
+}
+template <typename T> __device__ __forceinline__ T add_mod(T a, T b, T q) { return csub<T>(a + b, q); }
+template <typename T> __device__ __forceinline__ T sub_mod(T a, T b, T q) { return a >= b ? a - b : a + q - b; }
+
+}  // namespace gp

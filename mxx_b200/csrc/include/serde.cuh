@@ -1,0 +1,42 @@
+// serde.cuh — host u64 RNS words <-> device word-typed storage.
+//
+// Replaces serde_pack_u64_limb_to_packed_kernel / serde_unpack_packed_limb_to_u64_kernel
+// (cuda/src/matrix/MatrixSerde.cu:110, 137) and their per-limb staging + 2D-copy loop
+// (:566-741, :743-924).  The staging buffer holds the host layout [poly][limb][coeff]
+// u64 in natural slot order; the device keeps EVAL data bit-reversed, so the EVAL tag
+// applies the bit-reversal here (the only place natural order exists on the device).
+#pragma once
+#include "modarith.cuh"
+
+namespace gp {
+
+template <typename T, bool BITREV>
+__global__ void pack_kernel(T *__restrict__ dst, const uint64_t *__restrict__ src, size_t total, uint32_t logn) {
+    const size_t step = (size_t)gridDim.x * blockDim.x;
+    const uint32_t mask = (1u << logn) - 1;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
+        const uint32_t s = (uint32_t)i & mask;
+        const size_t j = BITREV ? ((i & ~(size_t)mask) | (__brev(s) >> (32 - logn))) : i;
+        dst[i] = (T)src[j];
+    }
+}
+
+template <typename T, bool BITREV>
+__global__ void unpack_kernel(uint64_t *__restrict__ dst, const T *__restrict__ src, size_t total, uint32_t logn) {
+    const size_t step = (size_t)gridDim.x * blockDim.x;
+    const uint32_t mask = (1u << logn) - 1;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
+        const uint32_t s = (uint32_t)i & mask;
+        const size_t j = BITREV ? ((i & ~(size_t)mask) | (__brev(s) >> (32 - logn))) : i;
+        dst[i] = (uint64_t)src[j];
+    }
+}
+
+// coefficient 0 of every (poly, limb): out[pl] = data[pl * n]
+template <typename T>
+__global__ void const_coeff_kernel(uint64_t *__restrict__ dst, const T *__restrict__ src, size_t count, uint32_t logn) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) dst[i] = (uint64_t)src[i << logn];
+}
+
+}  // namespace gp
