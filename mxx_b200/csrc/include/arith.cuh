@@ -12,10 +12,10 @@
 namespace gp {
 
 template <typename T, int V> struct alignas(sizeof(T) * V) Vec { T v[V]; };
-template <typename T, int V> __device__ __forceinline__ Vec<T, V> ldv(const T *p) {
+template <typename T, int V> GP_HD Vec<T, V> ldv(const T *p) {
     return *reinterpret_cast<const Vec<T, V> *>(p);
 }
-template <typename T, int V> __device__ __forceinline__ void stv(T *p, const Vec<T, V> &x) {
+template <typename T, int V> GP_HD void stv(T *p, const Vec<T, V> &x) {
     *reinterpret_cast<Vec<T, V> *>(p) = x;
 }
 
@@ -25,9 +25,9 @@ enum class EwOp { Add, Sub, MulScalar };
 template <typename T, int V, EwOp OP>
 __global__ void elementwise_kernel(T *__restrict__ out, const T *__restrict__ a, const T *__restrict__ b, size_t total,
                                    uint32_t limbs, uint32_t logn, const LimbConst<T> *__restrict__ lc) {
-    const size_t step = (size_t)gridDim.x * blockDim.x;
+    const size_t step = (size_t)gridDim.x * GP_NT;
     const size_t poly_words = (size_t)limbs << logn;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
+    for (size_t i = (size_t)blockIdx.x * GP_NT + GP_TID; i < total; i += step) {
         const size_t off = i * V;
         const uint32_t limb = (uint32_t)((off >> logn) % limbs);
         const LimbConst<T> c = lc[limb];
@@ -53,9 +53,9 @@ struct RectGeom {
 template <typename T, int V>
 __global__ void add_rect_kernel(T *__restrict__ dst, const T *__restrict__ src, RectGeom g, size_t total, uint32_t limbs,
                                 uint32_t logn, const LimbConst<T> *__restrict__ lc) {
-    const size_t step = (size_t)gridDim.x * blockDim.x;
+    const size_t step = (size_t)gridDim.x * GP_NT;
     const size_t poly_words = (size_t)limbs << logn;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
+    for (size_t i = (size_t)blockIdx.x * GP_NT + GP_TID; i < total; i += step) {
         const size_t off = i * V, rp = off / poly_words, w = off % poly_words;
         const size_t r = rp / g.cols, cc = rp % g.cols;
         const uint32_t limb = (uint32_t)(w >> logn);
@@ -69,43 +69,108 @@ __global__ void add_rect_kernel(T *__restrict__ dst, const T *__restrict__ src, 
     }
 }
 
+// dst block = src block (backs copy, copy_block, slice, concat, entry; replaces
+// block_copy_rect_all_limbs_kernel, MatrixArith.cu:88)
+template <typename T, int V>
+__global__ void copy_rect_kernel(T *__restrict__ dst, const T *__restrict__ src, RectGeom g, size_t total,
+                                 size_t poly_words) {
+    const size_t step = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
+        const size_t off = i * V, rp = off / poly_words, w = off % poly_words;
+        const size_t r = rp / g.cols, cc = rp % g.cols;
+        T *d = dst + ((g.dst_row + r) * g.dst_cols + g.dst_col + cc) * poly_words + w;
+        const T *s = src + ((g.src_row + r) * g.src_cols + g.src_col + cc) * poly_words + w;
+        stv<T, V>(d, ldv<T, V>(s));
+    }
+}
+
+// out (size x size) = rows [chunk*size, (chunk+1)*size) of identity(size, scalar).small_decompose():
+// global row gr = src_row*digits + digit holds scalar_by_digit[digit] at column src_row, zero elsewhere
+// (replaces matrix_fill_small_decomposed_identity_chunk_all_limbs_kernel, MatrixDecompose.cu:455-505).
+template <typename T, int V>
+__global__ void small_identity_chunk_kernel(T *__restrict__ out, const T *__restrict__ digits_row, size_t size,
+                                            size_t chunk_idx, size_t digits, size_t total, size_t poly_words) {
+    const size_t step = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
+        const size_t off = i * V, poly = off / poly_words, w = off % poly_words;
+        const size_t lr = poly / size, col = poly % size;
+        const size_t gr = chunk_idx * size + lr, src_row = gr / digits, digit = gr % digits;
+        Vec<T, V> x;
+        if (col == src_row) {
+            x = ldv<T, V>(digits_row + digit * poly_words + w);
+        } else {
+#pragma unroll
+            for (int k = 0; k < V; k++) x.v[k] = 0;
+        }
+        stv<T, V>(out + off, x);
+    }
+}
+
 template <typename T, int V>
 __global__ void equal_kernel(const T *__restrict__ a, const T *__restrict__ b, size_t total, int *__restrict__ diff) {
-    const size_t step = (size_t)gridDim.x * blockDim.x;
+    const size_t step = (size_t)gridDim.x * GP_NT;
     bool d = false;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
+    for (size_t i = (size_t)blockIdx.x * GP_NT + GP_TID; i < total; i += step) {
         Vec<T, V> x = ldv<T, V>(a + i * V), y = ldv<T, V>(b + i * V);
 #pragma unroll
         for (int k = 0; k < V; k++) d |= x.v[k] != y.v[k];
     }
-    if (__any_sync(0xffffffffu, d) && (threadIdx.x & 31) == 0) atomicOr(diff, 1);
+    if (__any_sync(0xffffffffu, d) && (GP_TID & 31) == 0) atomicOr(diff, 1);
 }
 
 // scalar fill of whole polys: out[poly][limb][*] = vals[poly*limbs + limb] (gadget matrix in EVAL form:
 // a constant polynomial evaluates to the constant at every slot).
 template <typename T>
 __global__ void fill_const_polys_kernel(T *__restrict__ out, const T *__restrict__ vals, size_t total_words, uint32_t logn) {
+    const size_t step = (size_t)gridDim.x * GP_NT;
+    for (size_t i = (size_t)blockIdx.x * GP_NT + GP_TID; i < total_words; i += step) out[i] = vals[i >> logn];
+}
+
+// Gadget matrix G = I_rows (x) g in EVAL form (a constant polynomial evaluates to the constant at
+// every slot): entry (row, row*ell + t*dpt + dg) holds pow[limb][dg] = 2^(bb*dg) mod q_limb in limb t
+// only (every limb when small), everything else is zero.  Replaces
+// matrix_fill_gadget_multi_limb_kernel + the NTT of a constant (MatrixDecompose.cu:212-252, 431-437).
+template <typename T>
+__global__ void gadget_fill_kernel(T *__restrict__ out, const T *__restrict__ pow, size_t total_words, uint32_t rows,
+                                   uint32_t ell, uint32_t dpt, uint32_t limbs, uint32_t logn, int small) {
     const size_t step = (size_t)gridDim.x * blockDim.x;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total_words; i += step) out[i] = vals[i >> logn];
+    const size_t cols = (size_t)rows * ell;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total_words; i += step) {
+        const size_t pl = i >> logn, poly = pl / limbs;
+        const uint32_t limb = (uint32_t)(pl % limbs);
+        const size_t row = poly / cols, col = poly % cols;
+        T v = 0;
+        if (col / ell == row) {
+            const uint32_t loc = (uint32_t)(col % ell), t = loc / dpt, dg = loc % dpt;
+            if (small || t == limb) v = pow[limb * dpt + dg];
+        }
+        out[i] = v;
+    }
 }
 
 // ---- matrix product ----------------------------------------------------------------
 // out(r x c) = A(r x k) * B(k x c), independently per (limb, slot).  A thread owns a
 // TR x TC tile of output polynomials at V consecutive slots of one limb.
-// grid: x = limbs * ceil(n / (V*blockDim.x)), y = ceil(c/TC), z = ceil(r/TR).
+// grid: x = limbs * ceil(n / (V*GP_NT)), y = ceil(c/TC), z = ceil(r/TR).
 // The product lands in columns [out_col0, out_col0 + cols) of an output with out_cols columns.
+struct MatmulGeom {
+    uint32_t rows, inner, cols;   // product shape (cols = columns computed by this launch)
+    uint32_t b_cols, b_col0;      // B has b_cols columns; the product uses [b_col0, b_col0 + cols)
+    uint32_t out_cols, out_col0;  // the product lands in columns [out_col0, out_col0 + cols) of out
+    uint32_t limbs, logn, fold;
+};
 template <typename T, int V, int TR, int TC>
-__global__ void __launch_bounds__(128)
-matmul_kernel(T *__restrict__ out, const T *__restrict__ A, const T *__restrict__ B, uint32_t rows, uint32_t inner,
-              uint32_t cols, uint32_t out_cols, uint32_t out_col0, uint32_t limbs, uint32_t logn, uint32_t fold,
-              const LimbConst<T> *__restrict__ lc) {
-    const uint32_t chunks = ((1u << logn) / V + blockDim.x - 1) / blockDim.x;
-    const uint32_t limb = blockIdx.x / chunks, chunk = blockIdx.x % chunks;
-    const uint32_t slot = (chunk * blockDim.x + threadIdx.x) * V;
+GP_HD void matmul_thread(uint32_t bx, uint32_t by, uint32_t bz, uint32_t tid, uint32_t ntid, T *__restrict__ out,
+                         const T *__restrict__ A, const T *__restrict__ B, const MatmulGeom &g,
+                         const LimbConst<T> *__restrict__ lc) {
+    const uint32_t rows = g.rows, inner = g.inner, cols = g.cols, limbs = g.limbs, logn = g.logn, fold = g.fold;
+    const uint32_t chunks = ((1u << logn) / V + ntid - 1) / ntid;
+    const uint32_t limb = bx / chunks, chunk = bx % chunks;
+    const uint32_t slot = (chunk * ntid + tid) * V;
     if (slot >= (1u << logn)) return;
     const size_t poly_words = (size_t)limbs << logn;
     const size_t in_poly = ((size_t)limb << logn) + slot;
-    const uint32_t r0 = blockIdx.z * TR, c0 = blockIdx.y * TC;
+    const uint32_t r0 = bz * TR, c0 = by * TC;
     const LimbConst<T> c = lc[limb];
 
     Acc<T> acc[TR][TC][V];
@@ -119,10 +184,10 @@ matmul_kernel(T *__restrict__ out, const T *__restrict__ A, const T *__restrict_
     // clamp out-of-range tile members onto valid polynomials; their results are not stored
     size_t arow[TR], bcol[TC];
 #pragma unroll
-    for (int i = 0; i < TR; i++) arow[i] = (size_t)min(r0 + i, rows - 1) * inner * poly_words + in_poly;
+    for (int i = 0; i < TR; i++) arow[i] = (size_t)(r0 + i < rows ? r0 + i : rows - 1) * inner * poly_words + in_poly;
 #pragma unroll
-    for (int j = 0; j < TC; j++) bcol[j] = (size_t)min(c0 + j, cols - 1) * poly_words + in_poly;
-    const size_t bstep = (size_t)cols * poly_words;
+    for (int j = 0; j < TC; j++) bcol[j] = (size_t)(g.b_col0 + (c0 + j < cols ? c0 + j : cols - 1)) * poly_words + in_poly;
+    const size_t bstep = (size_t)g.b_cols * poly_words;
 
     uint32_t since = 0;
 #pragma unroll 2
@@ -156,9 +221,15 @@ matmul_kernel(T *__restrict__ out, const T *__restrict__ A, const T *__restrict_
                 Vec<T, V> o;
 #pragma unroll
                 for (int v = 0; v < V; v++) o.v[v] = acc[i][j][v].result(c);
-                stv<T, V>(out + ((size_t)(r0 + i) * out_cols + out_col0 + c0 + j) * poly_words + in_poly, o);
+                stv<T, V>(out + ((size_t)(r0 + i) * g.out_cols + g.out_col0 + c0 + j) * poly_words + in_poly, o);
             }
         }
+}
+template <typename T, int V, int TR, int TC>
+__global__ void __launch_bounds__(128)
+matmul_kernel(T *__restrict__ out, const T *__restrict__ A, const T *__restrict__ B, MatmulGeom g,
+              const LimbConst<T> *__restrict__ lc) {
+    matmul_thread<T, V, TR, TC>(blockIdx.x, blockIdx.y, blockIdx.z, threadIdx.x, blockDim.x, out, A, B, g, lc);
 }
 
 }  // namespace gp

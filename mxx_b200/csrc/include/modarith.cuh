@@ -11,6 +11,23 @@
 #include <stdint.h>
 #include <cuda_runtime.h>
 
+// Block-level code is written against GP_TID / GP_NT / GP_SYNC so that the very same
+// templates also compile as host code, where they run as a ONE-thread block (every
+// strided loop then covers all its work items in order and the barrier is a no-op).
+// tests/ use that build (csrc/src/emu.cpp -> libgpupoly_emu.so) to check index math,
+// twiddle addressing and lazy-reduction bounds against the oracle without a GPU.
+// It is a test harness, not a CPU fallback: libgpupoly.so contains no host compute path.
+#ifdef __CUDA_ARCH__
+#define GP_TID threadIdx.x
+#define GP_NT blockDim.x
+#define GP_SYNC() __syncthreads()
+#else
+#define GP_TID 0u
+#define GP_NT 1u
+#define GP_SYNC() ((void)0)
+#endif
+#define GP_HD __host__ __device__ __forceinline__
+
 namespace gp {
 
 template <typename T> struct TwPair;
@@ -29,24 +46,47 @@ template <typename T> struct LimbConst {
     uint32_t pad;
 };
 
-__device__ __forceinline__ uint32_t mulhi(uint32_t a, uint32_t b) { return __umulhi(a, b); }
-__device__ __forceinline__ uint64_t mulhi(uint64_t a, uint64_t b) { return __umul64hi(a, b); }
+GP_HD uint32_t mulhi(uint32_t a, uint32_t b) {
+#ifdef __CUDA_ARCH__
+    return __umulhi(a, b);
+#else
+    return (uint32_t)(((uint64_t)a * b) >> 32);
+#endif
+}
+GP_HD uint64_t mulhi(uint64_t a, uint64_t b) {
+#ifdef __CUDA_ARCH__
+    return __umul64hi(a, b);
+#else
+    return (uint64_t)(((unsigned __int128)a * b) >> 64);
+#endif
+}
+GP_HD uint32_t brev32(uint32_t x) {
+#ifdef __CUDA_ARCH__
+    return __brev(x);
+#else
+    x = ((x >> 1) & 0x55555555u) | ((x & 0x55555555u) << 1);
+    x = ((x >> 2) & 0x33333333u) | ((x & 0x33333333u) << 2);
+    x = ((x >> 4) & 0x0f0f0f0fu) | ((x & 0x0f0f0f0fu) << 4);
+    x = ((x >> 8) & 0x00ff00ffu) | ((x & 0x00ff00ffu) << 8);
+    return (x >> 16) | (x << 16);
+#endif
+}
 
 // a*w mod q in [0, 2q) for ANY word a, w < q, ws = floor(w * 2^wordbits / q).
-template <typename T> __device__ __forceinline__ T mul_shoup_lazy(T a, T w, T ws, T q) {
+template <typename T> GP_HD T mul_shoup_lazy(T a, T w, T ws, T q) {
     T h = mulhi(a, ws);
     return a * w - h * q;
 }
-template <typename T> __device__ __forceinline__ T csub(T a, T q) { return a >= q ? a - q : a; }
+template <typename T> GP_HD T csub(T a, T q) { return a >= q ? a - q : a; }
 
 // x mod q for a 64-bit x (both widths use the 64-bit Barrett constant).
-template <typename T> __device__ __forceinline__ T red64(uint64_t x, const LimbConst<T> &c) {
-    uint64_t qh = __umul64hi(x, c.mu64);
+template <typename T> GP_HD T red64(uint64_t x, const LimbConst<T> &c) {
+    uint64_t qh = mulhi(x, c.mu64);
     uint64_t r = x - qh * (uint64_t)c.q;  // in [0, 2q)
     return (T)(r >= (uint64_t)c.q ? r - c.q : r);
 }
 // (hi*2^64 + lo) mod q, u64 limbs.
-__device__ __forceinline__ uint64_t red128(uint64_t hi, uint64_t lo, const LimbConst<uint64_t> &c) {
+GP_HD uint64_t red128(uint64_t hi, uint64_t lo, const LimbConst<uint64_t> &c) {
     uint64_t h = red64<uint64_t>(hi, c);
     uint64_t a = mul_shoup_lazy<uint64_t>(h, c.r64, c.r64_s, c.q);  // [0,2q)
     uint64_t b = red64<uint64_t>(lo, c);                             // [0,q)
@@ -59,34 +99,34 @@ __device__ __forceinline__ uint64_t red128(uint64_t hi, uint64_t lo, const LimbC
 template <typename T> struct Acc;
 template <> struct Acc<uint32_t> {
     uint64_t v;
-    __device__ __forceinline__ void clear() { v = 0; }
-    __device__ __forceinline__ void mac(uint32_t a, uint32_t b) { v += (uint64_t)a * b; }
+    GP_HD void clear() { v = 0; }
+    GP_HD void mac(uint32_t a, uint32_t b) { v += (uint64_t)a * b; }
     // products < 2^60: 16 terms fit 64 bits for q < 2^30
     static constexpr int kTermsPerFold = 16;
-    __device__ __forceinline__ void fold(const LimbConst<uint32_t> &c) { v = red64<uint32_t>(v, c); }
-    __device__ __forceinline__ uint32_t result(const LimbConst<uint32_t> &c) const { return red64<uint32_t>(v, c); }
+    GP_HD void fold(const LimbConst<uint32_t> &c) { v = red64<uint32_t>(v, c); }
+    GP_HD uint32_t result(const LimbConst<uint32_t> &c) const { return red64<uint32_t>(v, c); }
 };
 template <> struct Acc<uint64_t> {
     uint64_t lo, hi;
-    __device__ __forceinline__ void clear() { lo = 0; hi = 0; }
-    __device__ __forceinline__ void mac(uint64_t a, uint64_t b) {
-        uint64_t pl = a * b, ph = __umul64hi(a, b);
+    GP_HD void clear() { lo = 0; hi = 0; }
+    GP_HD void mac(uint64_t a, uint64_t b) {
+        uint64_t pl = a * b, ph = mulhi(a, b);
         lo += pl;
         hi += ph + (lo < pl);
     }
     // products < 2^124: 16 terms fit 128 bits for q < 2^62
     static constexpr int kTermsPerFold = 16;
-    __device__ __forceinline__ void fold(const LimbConst<uint64_t> &c) { lo = red128(hi, lo, c); hi = 0; }
-    __device__ __forceinline__ uint64_t result(const LimbConst<uint64_t> &c) const { return red128(hi, lo, c); }
+    GP_HD void fold(const LimbConst<uint64_t> &c) { lo = red128(hi, lo, c); hi = 0; }
+    GP_HD uint64_t result(const LimbConst<uint64_t> &c) const { return red128(hi, lo, c); }
 };
 
-template <typename T> __device__ __forceinline__ T mul_mod(T a, T b, const LimbConst<T> &c) {
+template <typename T> GP_HD T mul_mod(T a, T b, const LimbConst<T> &c) {
     Acc<T> acc;
     acc.clear();
     acc.mac(a, b);
     return acc.result(c);
 }
-template <typename T> __device__ __forceinline__ T add_mod(T a, T b, T q) { return csub<T>(a + b, q); }
-template <typename T> __device__ __forceinline__ T sub_mod(T a, T b, T q) { return a >= b ? a - b : a + q - b; }
+template <typename T> GP_HD T add_mod(T a, T b, T q) { return csub<T>(a + b, q); }
+template <typename T> GP_HD T sub_mod(T a, T b, T q) { return a >= b ? a - b : a + q - b; }
 
 }  // namespace gp

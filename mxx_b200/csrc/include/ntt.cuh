@@ -30,7 +30,7 @@ template <typename T> struct NttCfg {
     static constexpr int kMaxLogB = sizeof(T) == 4 ? 15 : 14;  // largest block held in smem
     static constexpr int kThreads = 512;
 };
-template <typename T> __device__ __forceinline__ uint32_t spad(uint32_t a) { return a + (a >> NttCfg<T>::kLogRow); }
+template <typename T> GP_HD uint32_t spad(uint32_t a) { return a + (a >> NttCfg<T>::kLogRow); }
 template <typename T> inline size_t ntt_smem_bytes(int logb) {
     size_t b = (size_t)1 << logb;
     return (b + (b >> NttCfg<T>::kLogRow) + 1) * sizeof(T);
@@ -39,7 +39,7 @@ template <typename T> inline size_t ntt_smem_bytes(int logb) {
 // Source functors: logical coefficient index -> value in [0, 4q).
 template <typename T> struct PlainSrc {
     const T *p;
-    __device__ __forceinline__ T operator()(uint32_t i) const { return p[i]; }
+    GP_HD T operator()(uint32_t i) const { return p[i]; }
 };
 // Gadget digit of a coefficient-form residue, the fused load of decompose + NTT:
 // (x_t >> dg*bb) & mask, reduced into the target limb if needed
@@ -49,7 +49,7 @@ template <typename T> struct DigitSrc {
     uint32_t shift;
     T mask;
     T q;
-    __device__ __forceinline__ T operator()(uint32_t i) const {
+    GP_HD T operator()(uint32_t i) const {
         T d = (p[i] >> shift) & mask;
         return d >= q ? d % q : d;
     }
@@ -60,7 +60,7 @@ template <typename T> struct DigitSrc {
 // Forward: x[j] sits at position base + j*stride; stage s pairs j and j + (R >> (s+1)).
 // twbase = (number of blocks before this pass) + (global block index).
 template <typename T, int LOGR>
-__device__ __forceinline__ void fwd_network(T (&x)[1 << LOGR], const TwPair<T> *__restrict__ tw, uint32_t twbase, T q, T q2) {
+GP_HD void fwd_network(T (&x)[1 << LOGR], const TwPair<T> *__restrict__ tw, uint32_t twbase, T q, T q2) {
     constexpr int R = 1 << LOGR;
 #pragma unroll
     for (int s = 0; s < LOGR; s++) {
@@ -83,7 +83,7 @@ __device__ __forceinline__ void fwd_network(T (&x)[1 << LOGR], const TwPair<T> *
 // Inverse: x[j] sits at position base + j*t0; stage s pairs j and j + (1 << s).
 // twbase = (number of blocks after this pass) + (global block index).
 template <typename T, int LOGR, bool FINAL>
-__device__ __forceinline__ void inv_network(T (&x)[1 << LOGR], const TwPair<T> *__restrict__ tw, uint32_t twbase,
+GP_HD void inv_network(T (&x)[1 << LOGR], const TwPair<T> *__restrict__ tw, uint32_t twbase,
                                             const LimbConst<T> &c) {
     constexpr int R = 1 << LOGR;
     const T q = c.q, q2 = c.q2;
@@ -120,11 +120,11 @@ __device__ __forceinline__ void inv_network(T (&x)[1 << LOGR], const TwPair<T> *
 // the whole transform (n / span).
 
 template <typename T, int LOGR, class Src>
-__device__ __forceinline__ void fwd_pass_from_src(const Src &src, T *sm, uint32_t logb, uint32_t nblk, uint32_t blk0,
+GP_HD void fwd_pass_from_src(const Src &src, T *sm, uint32_t logb, uint32_t nblk, uint32_t blk0,
                                                   const TwPair<T> *__restrict__ tw, T q, T q2) {
     constexpr int R = 1 << LOGR;
     const uint32_t lstride = logb - LOGR, stride = 1u << lstride, groups = 1u << lstride;
-    for (uint32_t g = threadIdx.x; g < groups; g += blockDim.x) {
+    for (uint32_t g = GP_TID; g < groups; g += GP_NT) {
         T x[R];
 #pragma unroll
         for (int j = 0; j < R; j++) x[j] = src(g + j * stride);
@@ -135,11 +135,11 @@ __device__ __forceinline__ void fwd_pass_from_src(const Src &src, T *sm, uint32_
 }
 
 template <typename T, int LOGR>
-__device__ __forceinline__ void fwd_pass_smem(T *sm, uint32_t logb, uint32_t lspan, uint32_t nblk, uint32_t blk0,
+GP_HD void fwd_pass_smem(T *sm, uint32_t logb, uint32_t lspan, uint32_t nblk, uint32_t blk0,
                                               const TwPair<T> *__restrict__ tw, T q, T q2) {
     constexpr int R = 1 << LOGR;
     const uint32_t lstride = lspan - LOGR, stride = 1u << lstride, groups = 1u << (logb - LOGR);
-    for (uint32_t g = threadIdx.x; g < groups; g += blockDim.x) {
+    for (uint32_t g = GP_TID; g < groups; g += GP_NT) {
         const uint32_t b = g >> lstride, e = g & (stride - 1), base = (b << lspan) + e;
         T x[R];
 #pragma unroll
@@ -151,11 +151,11 @@ __device__ __forceinline__ void fwd_pass_smem(T *sm, uint32_t logb, uint32_t lsp
 }
 
 template <typename T, int LOGR>
-__device__ __forceinline__ void inv_pass_smem(T *sm, uint32_t logb, uint32_t lt0, uint32_t nblk, uint32_t blk0,
+GP_HD void inv_pass_smem(T *sm, uint32_t logb, uint32_t lt0, uint32_t nblk, uint32_t blk0,
                                               const TwPair<T> *__restrict__ tw, const LimbConst<T> &c) {
     constexpr int R = 1 << LOGR;
     const uint32_t t0 = 1u << lt0, lspan = lt0 + LOGR, groups = 1u << (logb - LOGR);
-    for (uint32_t g = threadIdx.x; g < groups; g += blockDim.x) {
+    for (uint32_t g = GP_TID; g < groups; g += GP_NT) {
         const uint32_t b = g >> lt0, e = g & (t0 - 1), base = (b << lspan) + e;
         T x[R];
 #pragma unroll
@@ -168,11 +168,11 @@ __device__ __forceinline__ void inv_pass_smem(T *sm, uint32_t logb, uint32_t lt0
 
 // last inverse pass of a block: span == B, writes to global; FINAL merges n^-1.
 template <typename T, int LOGR, bool FINAL>
-__device__ __forceinline__ void inv_pass_to_dst(T *sm, T *__restrict__ dst, uint32_t logb, uint32_t nblk, uint32_t blk0,
+GP_HD void inv_pass_to_dst(T *sm, T *__restrict__ dst, uint32_t logb, uint32_t nblk, uint32_t blk0,
                                                 const TwPair<T> *__restrict__ tw, const LimbConst<T> &c) {
     constexpr int R = 1 << LOGR;
     const uint32_t lt0 = logb - LOGR, t0 = 1u << lt0, groups = t0;
-    for (uint32_t g = threadIdx.x; g < groups; g += blockDim.x) {
+    for (uint32_t g = GP_TID; g < groups; g += GP_NT) {
         T x[R];
 #pragma unroll
         for (int j = 0; j < R; j++) x[j] = sm[spad<T>(g + j * t0)];
@@ -187,7 +187,7 @@ __device__ __forceinline__ void inv_pass_to_dst(T *sm, T *__restrict__ dst, uint
 // Forward expects `top = logn - logb` stages already done by global passes.
 
 template <typename T, class Src>
-__device__ __forceinline__ void fwd_block(const Src &src, T *__restrict__ dst, T *sm, uint32_t logn, uint32_t logb,
+GP_HD void fwd_block(const Src &src, T *__restrict__ dst, T *sm, uint32_t logn, uint32_t logb,
                                           uint32_t sb, const TwPair<T> *__restrict__ tw, const LimbConst<T> &c) {
     constexpr int LR = NttCfg<T>::kLogR;
     const T q = c.q, q2 = c.q2;
@@ -204,14 +204,14 @@ __device__ __forceinline__ void fwd_block(const Src &src, T *__restrict__ dst, T
     }
     uint32_t lspan = logb - r;
     while (lspan > 0) {
-        __syncthreads();
+        GP_SYNC();
         const uint32_t per = logb - lspan;  // log2(span-blocks per CTA block)
         fwd_pass_smem<T, LR>(sm, logb, lspan, nblk << per, sb << per, tw, q, q2);
         lspan -= LR;
     }
-    __syncthreads();
+    GP_SYNC();
     const uint32_t B = 1u << logb;
-    for (uint32_t i = threadIdx.x; i < B; i += blockDim.x) {
+    for (uint32_t i = GP_TID; i < B; i += GP_NT) {
         T v = sm[spad<T>(i)];
         v = csub<T>(v, q2);
         dst[i] = csub<T>(v, q);
@@ -220,21 +220,21 @@ __device__ __forceinline__ void fwd_block(const Src &src, T *__restrict__ dst, T
 
 // Inverse: does the lowest logb stages of the block; FINAL (logb == logn) merges n^-1.
 template <typename T, bool FINAL>
-__device__ __forceinline__ void inv_block(const T *__restrict__ src, T *__restrict__ dst, T *sm, uint32_t logn,
+GP_HD void inv_block(const T *__restrict__ src, T *__restrict__ dst, T *sm, uint32_t logn,
                                           uint32_t logb, uint32_t sb, const TwPair<T> *__restrict__ tw,
                                           const LimbConst<T> &c) {
     constexpr int LR = NttCfg<T>::kLogR;
     const uint32_t B = 1u << logb;
-    for (uint32_t i = threadIdx.x; i < B; i += blockDim.x) sm[spad<T>(i)] = src[i];
+    for (uint32_t i = GP_TID; i < B; i += GP_NT) sm[spad<T>(i)] = src[i];
     const uint32_t r = logb % LR ? logb % LR : (logb < (uint32_t)LR ? logb : LR);  // last-pass radix
     uint32_t lt0 = 0;
     while (lt0 + r < logb) {
-        __syncthreads();
+        GP_SYNC();
         const uint32_t lspan = lt0 + LR;
         inv_pass_smem<T, LR>(sm, logb, lt0, 1u << (logn - lspan), sb << (logb - lspan), tw, c);
         lt0 += LR;
     }
-    __syncthreads();
+    GP_SYNC();
     const uint32_t nblk = 1u << (logn - logb);
     switch (r) {
         case 1: inv_pass_to_dst<T, 1, FINAL>(sm, dst, logb, nblk, sb, tw, c); break;
@@ -251,36 +251,44 @@ __device__ __forceinline__ void inv_block(const T *__restrict__ src, T *__restri
 // grid.x = polys * limbs * (n / B); data layout [poly][limb][n].
 
 template <typename T>
+GP_HD void ntt_fwd_cta(uint32_t bid, T *sm, const T *src, T *dst, uint32_t limbs, uint32_t logn, uint32_t logb,
+                       const TwPair<T> *__restrict__ tw_all, const LimbConst<T> *__restrict__ lc) {
+    const uint32_t lsub = logn - logb;
+    const size_t pl = bid >> lsub;
+    const uint32_t sb = bid & ((1u << lsub) - 1), limb = (uint32_t)(pl % limbs);
+    const size_t off = (pl << logn) + ((size_t)sb << logb);
+    const LimbConst<T> c = lc[limb];
+    PlainSrc<T> s{src + off};
+    fwd_block<T>(s, dst + off, sm, logn, logb, sb, tw_all + ((size_t)limb << logn), c);
+}
+template <typename T>
 __global__ void __launch_bounds__(NttCfg<T>::kThreads)
-ntt_fwd_kernel(T *data, uint32_t limbs, uint32_t logn, uint32_t logb, const TwPair<T> *__restrict__ tw_all,
+ntt_fwd_kernel(const T *src, T *dst, uint32_t limbs, uint32_t logn, uint32_t logb, const TwPair<T> *__restrict__ tw_all,
                const LimbConst<T> *__restrict__ lc) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    T *sm = reinterpret_cast<T *>(smem_raw);
-    const uint32_t lsub = logn - logb;
-    const size_t pl = blockIdx.x >> lsub;
-    const uint32_t sb = blockIdx.x & ((1u << lsub) - 1), limb = (uint32_t)(pl % limbs);
-    T *base = data + (pl << logn) + ((size_t)sb << logb);
-    const LimbConst<T> c = lc[limb];
-    PlainSrc<T> src{base};
-    fwd_block<T>(src, base, sm, logn, logb, sb, tw_all + ((size_t)limb << logn), c);
+    ntt_fwd_cta<T>(blockIdx.x, reinterpret_cast<T *>(smem_raw), src, dst, limbs, logn, logb, tw_all, lc);
 }
 
 template <typename T>
-__global__ void __launch_bounds__(NttCfg<T>::kThreads)
-ntt_inv_kernel(T *data, uint32_t limbs, uint32_t logn, uint32_t logb, const TwPair<T> *__restrict__ tw_all,
-               const LimbConst<T> *__restrict__ lc) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    T *sm = reinterpret_cast<T *>(smem_raw);
+GP_HD void ntt_inv_cta(uint32_t bid, T *sm, const T *src, T *dst, uint32_t limbs, uint32_t logn, uint32_t logb,
+                       const TwPair<T> *__restrict__ tw_all, const LimbConst<T> *__restrict__ lc) {
     const uint32_t lsub = logn - logb;
-    const size_t pl = blockIdx.x >> lsub;
-    const uint32_t sb = blockIdx.x & ((1u << lsub) - 1), limb = (uint32_t)(pl % limbs);
-    T *base = data + (pl << logn) + ((size_t)sb << logb);
+    const size_t pl = bid >> lsub;
+    const uint32_t sb = bid & ((1u << lsub) - 1), limb = (uint32_t)(pl % limbs);
+    const size_t off = (pl << logn) + ((size_t)sb << logb);
     const LimbConst<T> c = lc[limb];
     const TwPair<T> *tw = tw_all + ((size_t)limb << logn);
     if (lsub == 0)
-        inv_block<T, true>(base, base, sm, logn, logb, sb, tw, c);
+        inv_block<T, true>(src + off, dst + off, sm, logn, logb, sb, tw, c);
     else
-        inv_block<T, false>(base, base, sm, logn, logb, sb, tw, c);
+        inv_block<T, false>(src + off, dst + off, sm, logn, logb, sb, tw, c);
+}
+template <typename T>
+__global__ void __launch_bounds__(NttCfg<T>::kThreads)
+ntt_inv_kernel(const T *src, T *dst, uint32_t limbs, uint32_t logn, uint32_t logb, const TwPair<T> *__restrict__ tw_all,
+               const LimbConst<T> *__restrict__ lc) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    ntt_inv_cta<T>(blockIdx.x, reinterpret_cast<T *>(smem_raw), src, dst, limbs, logn, logb, tw_all, lc);
 }
 
 // Fused gadget decomposition + forward NTT: out row row*ell + t*dpt + dg, every limb
@@ -297,14 +305,12 @@ struct DecompGeom {
     uint32_t base_bits;
 };
 template <typename T, bool TO_EVAL>
-__global__ void __launch_bounds__(NttCfg<T>::kThreads)
-decompose_kernel(const T *__restrict__ src, T *__restrict__ out, DecompGeom g, uint32_t logn, uint32_t logb,
-                 const TwPair<T> *__restrict__ tw_all, const LimbConst<T> *__restrict__ lc) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    T *sm = reinterpret_cast<T *>(smem_raw);
+GP_HD void decompose_cta(uint32_t bid, T *sm, const T *__restrict__ src, T *__restrict__ out, const DecompGeom &g,
+                         uint32_t logn, uint32_t logb, const TwPair<T> *__restrict__ tw_all,
+                         const LimbConst<T> *__restrict__ lc) {
     const uint32_t lsub = logn - logb;
-    const size_t pl = blockIdx.x >> lsub;  // out (poly, limb)
-    const uint32_t sb = blockIdx.x & ((1u << lsub) - 1);
+    const size_t pl = bid >> lsub;  // out (poly, limb)
+    const uint32_t sb = bid & ((1u << lsub) - 1);
     const uint32_t limb = (uint32_t)(pl % g.limbs);
     const size_t opoly = pl / g.limbs;
     const size_t orow = opoly / g.cols, col = opoly % g.cols;
@@ -315,7 +321,7 @@ decompose_kernel(const T *__restrict__ src, T *__restrict__ out, DecompGeom g, u
     T mask = 0;
     if (shift < sbits) {
         const uint32_t rem = sbits - shift, db = g.base_bits < rem ? g.base_bits : rem;
-        mask = db >= sizeof(T) * 8 ? ~(T)0 : (((T)1 << db) - 1);
+        mask = db >= sizeof(T) * 8 ? ~(T)0 : (T)(((T)1 << db) - 1);
     }
     const T *sp = src + (((row * g.src_cols + g.src_col0 + col) * g.limbs + t) << logn) + ((size_t)sb << logb);
     T *dp = out + (pl << logn) + ((size_t)sb << logb);
@@ -324,18 +330,24 @@ decompose_kernel(const T *__restrict__ src, T *__restrict__ out, DecompGeom g, u
         fwd_block<T>(dsrc, dp, sm, logn, logb, sb, tw_all + ((size_t)limb << logn), c);
     } else {
         const uint32_t B = 1u << logb;
-        for (uint32_t i = threadIdx.x; i < B; i += blockDim.x) dp[i] = dsrc(i);
+        for (uint32_t i = GP_TID; i < B; i += GP_NT) dp[i] = dsrc(i);
     }
+}
+template <typename T, bool TO_EVAL>
+__global__ void __launch_bounds__(NttCfg<T>::kThreads)
+decompose_kernel(const T *__restrict__ src, T *__restrict__ out, DecompGeom g, uint32_t logn, uint32_t logb,
+                 const TwPair<T> *__restrict__ tw_all, const LimbConst<T> *__restrict__ lc) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    decompose_cta<T, TO_EVAL>(blockIdx.x, reinterpret_cast<T *>(smem_raw), src, out, g, logn, logb, tw_all, lc);
 }
 
 // ---- global radix passes for n larger than one CTA's shared memory --------------------
 // Forward top pass: stages with span in (B, n]; one thread per radix-R group.
 template <typename T, int LOGR>
-__global__ void ntt_fwd_global_pass(T *data, uint32_t limbs, uint32_t logn, uint32_t lspan,
-                                    const TwPair<T> *__restrict__ tw_all, const LimbConst<T> *__restrict__ lc) {
+GP_HD void fwd_global_thread(size_t gid, T *data, uint32_t limbs, uint32_t logn, uint32_t lspan,
+                             const TwPair<T> *__restrict__ tw_all, const LimbConst<T> *__restrict__ lc) {
     constexpr int R = 1 << LOGR;
-    const uint32_t lg = logn - LOGR;  // groups per transform
-    const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t lg = logn - LOGR;  // log2(groups per transform)
     const size_t pl = gid >> lg;
     const uint32_t g = (uint32_t)(gid & ((1u << lg) - 1)), limb = (uint32_t)(pl % limbs);
     const uint32_t lstride = lspan - LOGR, stride = 1u << lstride;
@@ -347,15 +359,21 @@ __global__ void ntt_fwd_global_pass(T *data, uint32_t limbs, uint32_t logn, uint
     for (int j = 0; j < R; j++) x[j] = base[(size_t)j * stride];
     fwd_network<T, LOGR>(x, tw_all + ((size_t)limb << logn), (1u << (logn - lspan)) + b, c.q, c.q2);
 #pragma unroll
-    for (int j = 0; j < R; j++) base[(size_t)j * stride] = x[j];  // lazy [0,4q): next kernel accepts it
+    for (int j = 0; j < R; j++) base[(size_t)j * stride] = x[j];  // lazy [0,4q): the next pass accepts it
+}
+template <typename T, int LOGR>
+__global__ void __launch_bounds__(256)
+ntt_fwd_global_pass(T *data, size_t total, uint32_t limbs, uint32_t logn, uint32_t lspan,
+                    const TwPair<T> *__restrict__ tw_all, const LimbConst<T> *__restrict__ lc) {
+    const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid < total) fwd_global_thread<T, LOGR>(gid, data, limbs, logn, lspan, tw_all, lc);
 }
 // Inverse top pass: distances t0 .. t0*R/2 with t0 >= B; FINAL merges n^-1.
 template <typename T, int LOGR, bool FINAL>
-__global__ void ntt_inv_global_pass(T *data, uint32_t limbs, uint32_t logn, uint32_t lt0,
-                                    const TwPair<T> *__restrict__ tw_all, const LimbConst<T> *__restrict__ lc) {
+GP_HD void inv_global_thread(size_t gid, T *data, uint32_t limbs, uint32_t logn, uint32_t lt0,
+                             const TwPair<T> *__restrict__ tw_all, const LimbConst<T> *__restrict__ lc) {
     constexpr int R = 1 << LOGR;
     const uint32_t lg = logn - LOGR;
-    const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     const size_t pl = gid >> lg;
     const uint32_t g = (uint32_t)(gid & ((1u << lg) - 1)), limb = (uint32_t)(pl % limbs);
     const uint32_t t0 = 1u << lt0, lspan = lt0 + LOGR;
@@ -369,5 +387,27 @@ __global__ void ntt_inv_global_pass(T *data, uint32_t limbs, uint32_t logn, uint
 #pragma unroll
     for (int j = 0; j < R; j++) base[(size_t)j * t0] = FINAL ? csub<T>(x[j], c.q) : x[j];
 }
+template <typename T, int LOGR, bool FINAL>
+__global__ void __launch_bounds__(256)
+ntt_inv_global_pass(T *data, size_t total, uint32_t limbs, uint32_t logn, uint32_t lt0,
+                    const TwPair<T> *__restrict__ tw_all, const LimbConst<T> *__restrict__ lc) {
+    const size_t gid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid < total) inv_global_thread<T, LOGR, FINAL>(gid, data, limbs, logn, lt0, tw_all, lc);
+}
+
+// ---- host-side schedule shared by the launcher (MatrixNTT.inl) and the emulation harness ----
+template <typename T> inline int ntt_block_log(int logn) { return logn < NttCfg<T>::kMaxLogB ? logn : NttCfg<T>::kMaxLogB; }
+// Splits `top` stages into passes of at most 4 stages (16 strided words per thread keep
+// every 32-byte sector of the global accesses fully used for stride >= 8 words).
+inline void split_top(int top, int *passes, int *count) {
+    *count = 0;
+    while (top > 0) {
+        int r = top >= 4 ? 4 : top;
+        if (top > 4 && top < 8 && top - r < 2) r = top - 2;  // avoid a trailing radix-2 pass
+        passes[(*count)++] = r;
+        top -= r;
+    }
+}
+
 
 }  // namespace gp

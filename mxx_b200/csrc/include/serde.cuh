@@ -12,22 +12,22 @@ namespace gp {
 
 template <typename T, bool BITREV>
 __global__ void pack_kernel(T *__restrict__ dst, const uint64_t *__restrict__ src, size_t total, uint32_t logn) {
-    const size_t step = (size_t)gridDim.x * blockDim.x;
+    const size_t step = (size_t)gridDim.x * GP_NT;
     const uint32_t mask = (1u << logn) - 1;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
+    for (size_t i = (size_t)blockIdx.x * GP_NT + GP_TID; i < total; i += step) {
         const uint32_t s = (uint32_t)i & mask;
-        const size_t j = BITREV ? ((i & ~(size_t)mask) | (__brev(s) >> (32 - logn))) : i;
+        const size_t j = BITREV ? ((i & ~(size_t)mask) | (brev32(s) >> (32 - logn))) : i;
         dst[i] = (T)src[j];
     }
 }
 
 template <typename T, bool BITREV>
 __global__ void unpack_kernel(uint64_t *__restrict__ dst, const T *__restrict__ src, size_t total, uint32_t logn) {
-    const size_t step = (size_t)gridDim.x * blockDim.x;
+    const size_t step = (size_t)gridDim.x * GP_NT;
     const uint32_t mask = (1u << logn) - 1;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
+    for (size_t i = (size_t)blockIdx.x * GP_NT + GP_TID; i < total; i += step) {
         const uint32_t s = (uint32_t)i & mask;
-        const size_t j = BITREV ? ((i & ~(size_t)mask) | (__brev(s) >> (32 - logn))) : i;
+        const size_t j = BITREV ? ((i & ~(size_t)mask) | (brev32(s) >> (32 - logn))) : i;
         dst[i] = (uint64_t)src[j];
     }
 }
@@ -35,7 +35,7 @@ __global__ void unpack_kernel(uint64_t *__restrict__ dst, const T *__restrict__ 
 // coefficient 0 of every (poly, limb): out[pl] = data[pl * n]
 template <typename T>
 __global__ void const_coeff_kernel(uint64_t *__restrict__ dst, const T *__restrict__ src, size_t count, uint32_t logn) {
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t i = (size_t)blockIdx.x * GP_NT + GP_TID;
     if (i < count) dst[i] = (uint64_t)src[i << logn];
 }
 

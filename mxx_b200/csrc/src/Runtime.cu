@@ -14,6 +14,7 @@
 #include <unordered_set>
 
 #include "gpupoly_internal.cuh"
+#include "host_tables.hpp"
 
 namespace gp {
 static thread_local std::string t_last_error;
@@ -34,110 +35,22 @@ int set_cuda_error(cudaError_t err, const char *where) {
 }  // namespace gp
 
 namespace {
-typedef unsigned __int128 u128;
-
-uint64_t mulmod(uint64_t a, uint64_t b, uint64_t q) { return (uint64_t)(((u128)a * b) % q); }
-uint64_t powmod(uint64_t b, uint64_t e, uint64_t q) {
-    uint64_t r = 1 % q, c = b % q;
-    for (; e; e >>= 1) {
-        if (e & 1) r = mulmod(r, c, q);
-        c = mulmod(c, c, q);
-    }
-    return r;
-}
-bool invmod(uint64_t a, uint64_t q, uint64_t &out) {
-    __int128 t = 0, nt = 1, r = q, nr = a % q;
-    while (nr != 0) {
-        __int128 k = r / nr, tmp = t - k * nt;
-        t = nt; nt = tmp;
-        tmp = r - k * nr; r = nr; nr = tmp;
-    }
-    if (r != 1) return false;
-    if (t < 0) t += q;
-    out = (uint64_t)t;
-    return true;
-}
-// distinct prime factors of m (trial division; 2 stripped first, odd candidates after)
-std::vector<uint64_t> prime_factors(uint64_t m) {
-    std::vector<uint64_t> f;
-    if ((m & 1) == 0) {
-        f.push_back(2);
-        while ((m & 1) == 0) m >>= 1;
-    }
-    for (uint64_t d = 3; d * d <= m; d += 2) {
-        if (m % d) continue;
-        f.push_back(d);
-        while (m % d == 0) m /= d;
-    }
-    if (m > 1) f.push_back(m);
-    return f;
-}
-// least primitive root — same value the reference finds (Runtime.cu:121-165)
-uint64_t least_primitive_root(uint64_t p) {
-    const uint64_t phi = p - 1;
-    const std::vector<uint64_t> fac = prime_factors(phi);
-    for (uint64_t g = 2; g < p; ++g) {
-        bool ok = true;
-        for (uint64_t f : fac)
-            if (powmod(g, phi / f, p) == 1) { ok = false; break; }
-        if (ok) return g;
-    }
-    throw std::runtime_error("failed to find primitive root");
-}
-uint64_t primitive_2n_root(uint64_t p, uint64_t n) {  // Runtime.cu:167-190
-    const uint64_t order = 2 * n;
-    if (p % order != 1) throw std::runtime_error("modulus is not congruent to 1 mod 2N");
-    const uint64_t root = powmod(least_primitive_root(p), (p - 1) / order, p);
-    if (powmod(root, n, p) != p - 1) throw std::runtime_error("computed root is not a primitive 2N-th root");
-    return root;
-}
-uint32_t bitrev(uint32_t x, int bits) { return bits == 0 ? 0 : (__builtin_bitreverse32(x) >> (32 - bits)); }
-
-template <typename T> T shoup(uint64_t w, uint64_t q) { return (T)((((u128)w) << (sizeof(T) * 8)) / q); }
+using namespace gp::host;
 
 template <typename T>
-void build_tables(GpuContext *ctx) {
-    const size_t n = (size_t)ctx->N, L = ctx->moduli.size();
-    std::vector<gp::TwPair<T>> fwd(L * n), inv(L * n);
-    std::vector<gp::LimbConst<T>> lc(L);
-    for (size_t l = 0; l < L; ++l) {
-        const uint64_t q = ctx->moduli[l], psi = ctx->psi[l];
-        uint64_t ipsi = 0, ninv = 0;
-        if (!invmod(psi, q, ipsi) || !invmod(n % q, q, ninv)) throw std::runtime_error("failed to invert NTT constants");
-        uint64_t w = 1, iw = 1;
-        for (size_t i = 0; i < n; ++i) {
-            const size_t r = bitrev((uint32_t)i, ctx->logN);
-            fwd[l * n + r] = {(T)w, shoup<T>(w, q)};
-            inv[l * n + r] = {(T)iw, shoup<T>(iw, q)};
-            w = mulmod(w, psi, q);
-            iw = mulmod(iw, ipsi, q);
-        }
-        gp::LimbConst<T> &c = lc[l];
-        c.q = (T)q;
-        c.q2 = (T)(2 * q);
-        c.ninv = (T)ninv;
-        c.ninv_s = shoup<T>(ninv, q);
-        const uint64_t nw = mulmod(ninv, n > 1 ? (uint64_t)inv[l * n + 1].w : 1, q);
-        c.nw = (T)nw;
-        c.nw_s = shoup<T>(nw, q);
-        const uint64_t r64 = (uint64_t)((((u128)1) << 64) % q);
-        c.r64 = (T)r64;
-        c.r64_s = shoup<T>(r64, q);
-        c.mu64 = (uint64_t)((((u128)1) << 64) / q);
-        c.bits = 64 - (uint32_t)__builtin_clzll(q);
-        c.pad = 0;
-    }
+void upload_tables(GpuContext *ctx) {
+    const Tables<T> t = build_tables<T>(ctx->logN, ctx->moduli, ctx->psi);
     void *d_fwd = nullptr, *d_inv = nullptr, *d_lc = nullptr;
     auto chk = [](cudaError_t e) { if (e != cudaSuccess) throw std::runtime_error(cudaGetErrorString(e)); };
-    chk(cudaMalloc(&d_fwd, fwd.size() * sizeof(fwd[0])));
+    chk(cudaMalloc(&d_fwd, t.fwd.size() * sizeof(t.fwd[0])));
     ctx->d_fwd = d_fwd;
-    chk(cudaMalloc(&d_inv, inv.size() * sizeof(inv[0])));
+    chk(cudaMalloc(&d_inv, t.inv.size() * sizeof(t.inv[0])));
     ctx->d_inv = d_inv;
-    chk(cudaMalloc(&d_lc, lc.size() * sizeof(lc[0])));
+    chk(cudaMalloc(&d_lc, t.limb.size() * sizeof(t.limb[0])));
     ctx->d_limb = d_lc;
-    chk(cudaMemcpy(d_fwd, fwd.data(), fwd.size() * sizeof(fwd[0]), cudaMemcpyHostToDevice));
-    chk(cudaMemcpy(d_inv, inv.data(), inv.size() * sizeof(inv[0]), cudaMemcpyHostToDevice));
-    chk(cudaMemcpy(d_lc, lc.data(), lc.size() * sizeof(lc[0]), cudaMemcpyHostToDevice));
+    chk(cudaMemcpy(d_fwd, t.fwd.data(), t.fwd.size() * sizeof(t.fwd[0]), cudaMemcpyHostToDevice));
+    chk(cudaMemcpy(d_inv, t.inv.data(), t.inv.size() * sizeof(t.inv[0]), cudaMemcpyHostToDevice));
+    chk(cudaMemcpy(d_lc, t.limb.data(), t.limb.size() * sizeof(t.limb[0]), cudaMemcpyHostToDevice));
 }
 
 void free_context(GpuContext *ctx) {
@@ -204,21 +117,16 @@ int gpu_context_create(uint32_t logN, uint32_t L, uint32_t dnum, const uint64_t 
             ctx->psi.push_back(primitive_2n_root(q, (uint64_t)ctx->N));
         }
         ctx->crt_bits = 64 - (uint32_t)__builtin_clzll(qmax);
-        ctx->wide = qmax >= (1ull << 30);
-        {  // products that fit a lazy accumulator (2^64 resp. 2^128) on top of one folded residue
-            const u128 q2 = (u128)(qmax - 1) * (qmax - 1);
-            const u128 room = ctx->wide ? (~(u128)0 - qmax) : ((u128)~0ull - qmax);
-            u128 terms = room / q2;
-            ctx->mac_fold = (uint32_t)std::min<u128>(std::max<u128>(terms, 1), 1u << 16);
-        }
+        ctx->wide = needs_wide(qmax);
+        ctx->mac_fold = mac_fold_terms(qmax, ctx->wide);
         GP_CUDA(cudaSetDevice(ctx->device), "cudaSetDevice");
         cudaDeviceProp prop;
         GP_CUDA(cudaGetDeviceProperties(&prop, ctx->device), "cudaGetDeviceProperties");
         ctx->sm_count = prop.multiProcessorCount;
         ctx->max_smem_optin = (int)prop.sharedMemPerBlockOptin;
         GP_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking), "cudaStreamCreate");
-        if (ctx->wide) build_tables<uint64_t>(ctx);
-        else build_tables<uint32_t>(ctx);
+        if (ctx->wide) upload_tables<uint64_t>(ctx);
+        else upload_tables<uint32_t>(ctx);
         *out_ctx = ctx;
         return 0;
     } catch (const std::exception &e) {

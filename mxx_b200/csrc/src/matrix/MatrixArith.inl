@@ -1,0 +1,186 @@
+// MatrixArith.inl — add / sub / add_block / mul / mul_scalar / equal.
+// Replaces cuda/src/matrix/MatrixArith.cu (gpu_matrix_add :2632, add_block :2698, sub
+// :2774, mul :2840-2907, equal :2909, mul_scalar :2982): every op is ONE launch over all
+// limbs on the context stream; nothing is uploaded per call.
+
+namespace {
+
+template <typename T, gp::EwOp OP>
+int launch_elementwise(GpuContext *ctx, T *out, const T *a, const T *b, size_t words, uint32_t limbs) {
+    if (words == 0) return 0;
+    const int V = vec_width<T>(ctx);
+    const size_t total = words / V;
+    const unsigned threads = 256, grid = stride_grid(ctx, total, threads);
+    const auto *lc = (const gp::LimbConst<T> *)ctx->d_limb;
+    const uint32_t logn = (uint32_t)ctx->logN;
+    switch (V) {
+        case 4: gp::elementwise_kernel<T, 4, OP><<<grid, threads, 0, ctx->stream>>>(out, a, b, total, limbs, logn, lc); break;
+        case 2: gp::elementwise_kernel<T, 2, OP><<<grid, threads, 0, ctx->stream>>>(out, a, b, total, limbs, logn, lc); break;
+        default: gp::elementwise_kernel<T, 1, OP><<<grid, threads, 0, ctx->stream>>>(out, a, b, total, limbs, logn, lc); break;
+    }
+    gp::count_launch();
+    GP_CHECK_LAUNCH("elementwise_kernel");
+    return 0;
+}
+
+template <typename T, int V, int TR, int TC>
+int launch_matmul_tile(GpuContext *ctx, T *out, const T *A, const T *B, const gp::MatmulGeom &g) {
+    const unsigned threads = 128;
+    const unsigned per_limb = (unsigned)(((size_t)ctx->N / V + threads - 1) / threads);
+    dim3 grid(g.limbs * per_limb, (g.cols + TC - 1) / TC, (g.rows + TR - 1) / TR);
+    gp::matmul_kernel<T, V, TR, TC><<<grid, threads, 0, ctx->stream>>>(out, A, B, g, (const gp::LimbConst<T> *)ctx->d_limb);
+    gp::count_launch();
+    GP_CHECK_LAUNCH("matmul_kernel");
+    return 0;
+}
+
+// out[:, out_col0 : out_col0+cols] = A(rows x inner) * B[:, b_col0 : b_col0+cols]
+template <typename T> int run_matmul(GpuContext *ctx, T *out, const T *A, const T *B, gp::MatmulGeom g) {
+    if (g.rows == 0 || g.cols == 0 || g.limbs == 0) return 0;
+    g.logn = (uint32_t)ctx->logN;
+    g.fold = ctx->mac_fold;
+    constexpr int VMAX = 16 / (int)sizeof(T);
+    const int V = vec_width<T>(ctx);
+    if (g.inner == 0) {  // empty sum: the zero matrix
+        for (uint32_t r = 0; r < g.rows; r++)
+            GP_CUDA(cudaMemsetAsync(out + ((size_t)r * g.out_cols + g.out_col0) * ((size_t)g.limbs << g.logn), 0,
+                                    (size_t)g.cols * ((size_t)g.limbs << g.logn) * sizeof(T), ctx->stream),
+                    "cudaMemsetAsync(matmul)");
+        return 0;
+    }
+    if (V != VMAX) return launch_matmul_tile<T, 1, 1, 1>(ctx, out, A, B, g);  // tiny rings (n < 16 bytes of words)
+    // Register tile: the wider the tile the fewer operand loads per product.  rows == 1 (the
+    // BGG / bench_matrix_mul shape) streams B once and re-reads A from L2.
+    if (g.rows >= 4) return launch_matmul_tile<T, VMAX / 2, 4, 4>(ctx, out, A, B, g);
+    if (g.rows >= 2) return launch_matmul_tile<T, VMAX, 2, 4>(ctx, out, A, B, g);
+    return launch_matmul_tile<T, VMAX, 1, 4>(ctx, out, A, B, g);
+}
+
+int binary_check(const char *name, GpuMatrix *out, const GpuMatrix *lhs, const GpuMatrix *rhs) {
+    if (!out || !lhs || !rhs) return gp::set_error(std::string("invalid ") + name + " arguments");
+    if (!same_ctx(out, lhs) || !same_ctx(out, rhs)) return gp::set_error(std::string("context mismatch in ") + name);
+    return 0;
+}
+}  // namespace
+
+extern "C" int gpu_matrix_add(GpuMatrix *out, const GpuMatrix *lhs, const GpuMatrix *rhs) {
+    if (binary_check("gpu_matrix_add", out, lhs, rhs)) return 1;
+    if (!same_shape(lhs, rhs) || !same_shape(out, lhs)) return gp::set_error("size mismatch in gpu_matrix_add");
+    GpuContext *ctx = out->ctx;
+    if (bind_device(ctx)) return 1;
+    const size_t words = out->polys() * out->poly_words();
+    int st = GP_DISPATCH_WIDTH(ctx, return (launch_elementwise<T, gp::EwOp::Add>(ctx, (T *)out->data, (const T *)lhs->data,
+                                                                                 (const T *)rhs->data, words, (uint32_t)out->limbs())););
+    // the reference marks the result EVAL unconditionally (MatrixArith.cu:2694) while its Rust
+    // side tracks the domain itself; propagating the operands' domain is a superset of that
+    if (!st) out->format = lhs->format;
+    return st;
+}
+
+extern "C" int gpu_matrix_sub(GpuMatrix *out, const GpuMatrix *lhs, const GpuMatrix *rhs) {
+    if (binary_check("gpu_matrix_sub", out, lhs, rhs)) return 1;
+    if (!same_shape(lhs, rhs) || !same_shape(out, lhs)) return gp::set_error("size mismatch in gpu_matrix_sub");
+    GpuContext *ctx = out->ctx;
+    if (bind_device(ctx)) return 1;
+    const size_t words = out->polys() * out->poly_words();
+    int st = GP_DISPATCH_WIDTH(ctx, return (launch_elementwise<T, gp::EwOp::Sub>(ctx, (T *)out->data, (const T *)lhs->data,
+                                                                                 (const T *)rhs->data, words, (uint32_t)out->limbs())););
+    if (!st) out->format = lhs->format;
+    return st;
+}
+
+extern "C" int gpu_matrix_mul_scalar(GpuMatrix *out, const GpuMatrix *lhs, const GpuMatrix *scalar) {
+    if (binary_check("gpu_matrix_mul_scalar", out, lhs, scalar)) return 1;
+    if (scalar->rows != 1 || scalar->cols != 1) return gp::set_error("scalar must be 1x1 in gpu_matrix_mul_scalar");
+    if (!same_shape(out, lhs)) return gp::set_error("size mismatch in gpu_matrix_mul_scalar");
+    if (lhs->format != GPU_POLY_FORMAT_EVAL || scalar->format != GPU_POLY_FORMAT_EVAL)
+        return gp::set_error("gpu_matrix_mul_scalar requires EVAL format");  // MatrixArith.cu:3011-3014
+    GpuContext *ctx = out->ctx;
+    if (bind_device(ctx)) return 1;
+    const size_t words = out->polys() * out->poly_words();
+    int st = GP_DISPATCH_WIDTH(ctx, return (launch_elementwise<T, gp::EwOp::MulScalar>(
+                                        ctx, (T *)out->data, (const T *)lhs->data, (const T *)scalar->data, words, (uint32_t)out->limbs())););
+    if (!st) out->format = GPU_POLY_FORMAT_EVAL;
+    return st;
+}
+
+extern "C" int gpu_matrix_add_block(GpuMatrix *out, const GpuMatrix *src, size_t dst_row, size_t dst_col, size_t src_row,
+                                    size_t src_col, size_t rows, size_t cols) {
+    if (!out || !src) return gp::set_error("invalid gpu_matrix_add_block arguments");
+    if (!same_ctx(out, src)) return gp::set_error("context mismatch in gpu_matrix_add_block");
+    if (src_row + rows > src->rows || src_col + cols > src->cols || dst_row + rows > out->rows ||
+        dst_col + cols > out->cols)
+        return gp::set_error("block out of range in gpu_matrix_add_block");
+    if (rows == 0 || cols == 0 || out->level < 0) return 0;
+    GpuContext *ctx = out->ctx;
+    if (bind_device(ctx)) return 1;
+    const gp::RectGeom g{out->cols, src->cols, dst_row, dst_col, src_row, src_col, rows, cols};
+    return GP_DISPATCH_WIDTH(
+        ctx, const int V = vec_width<T>(ctx); const size_t total = rows * cols * out->poly_words() / V;
+        const unsigned threads = 256, grid = stride_grid(ctx, total, threads);
+        const auto *lc = (const gp::LimbConst<T> *)ctx->d_limb; const uint32_t limbs = (uint32_t)out->limbs(), logn = (uint32_t)ctx->logN;
+        T *d = (T *)out->data; const T *s = (const T *)src->data;
+        switch (V) {
+            case 4: gp::add_rect_kernel<T, 4><<<grid, threads, 0, ctx->stream>>>(d, s, g, total, limbs, logn, lc); break;
+            case 2: gp::add_rect_kernel<T, 2><<<grid, threads, 0, ctx->stream>>>(d, s, g, total, limbs, logn, lc); break;
+            default: gp::add_rect_kernel<T, 1><<<grid, threads, 0, ctx->stream>>>(d, s, g, total, limbs, logn, lc); break;
+        } gp::count_launch();
+        GP_CHECK_LAUNCH("add_rect_kernel"); return 0;);
+}
+
+extern "C" int gpu_matrix_mul(GpuMatrix *out, const GpuMatrix *lhs, const GpuMatrix *rhs) {
+    if (binary_check("gpu_matrix_mul", out, lhs, rhs)) return 1;
+    if (lhs->cols != rhs->rows || out->rows != lhs->rows || out->cols != rhs->cols)
+        return gp::set_error("size mismatch in gpu_matrix_mul");
+    if (lhs->format != GPU_POLY_FORMAT_EVAL || rhs->format != GPU_POLY_FORMAT_EVAL)
+        return gp::set_error("gpu_matrix_mul requires EVAL format");  // MatrixArith.cu:2863-2866
+    if (out == lhs || out == rhs || (out->data && (out->data == lhs->data || out->data == rhs->data)))
+        return gp::set_error("gpu_matrix_mul output must not alias an input");
+    GpuContext *ctx = out->ctx;
+    out->format = GPU_POLY_FORMAT_EVAL;
+    if (out->polys() == 0 || out->level < 0) return 0;
+    if (bind_device(ctx)) return 1;
+    gp::MatmulGeom g{};
+    g.rows = (uint32_t)lhs->rows;
+    g.inner = (uint32_t)lhs->cols;
+    g.cols = (uint32_t)rhs->cols;
+    g.b_cols = (uint32_t)rhs->cols;
+    g.b_col0 = 0;
+    g.out_cols = (uint32_t)out->cols;
+    g.out_col0 = 0;
+    g.limbs = (uint32_t)out->limbs();
+    return GP_DISPATCH_WIDTH(ctx, return run_matmul<T>(ctx, (T *)out->data, (const T *)lhs->data, (const T *)rhs->data, g););
+}
+
+extern "C" int gpu_matrix_equal(const GpuMatrix *lhs, const GpuMatrix *rhs, int *out_equal) {
+    if (!lhs || !rhs || !out_equal) return gp::set_error("invalid gpu_matrix_equal arguments");
+    *out_equal = 0;
+    if (lhs->ctx != rhs->ctx || lhs->level != rhs->level || !same_shape(lhs, rhs)) return 0;
+    if (lhs->format != rhs->format) return 0;  // MatrixArith.cu:2934-2937: not equal, no error
+    GpuContext *ctx = lhs->ctx;
+    const size_t words = lhs->polys() * lhs->poly_words();
+    if (words == 0 || lhs->data == rhs->data) {
+        *out_equal = 1;
+        return 0;
+    }
+    if (bind_device(ctx)) return 1;
+    Scratch flag;
+    if (flag.alloc(sizeof(int), ctx->stream)) return 1;
+    GP_CUDA(cudaMemsetAsync(flag.p, 0, sizeof(int), ctx->stream), "cudaMemsetAsync(equal)");
+    int st = GP_DISPATCH_WIDTH(
+        ctx, const int V = vec_width<T>(ctx); const size_t total = words / V;
+        const unsigned threads = 256, grid = stride_grid(ctx, total, threads);
+        const T *a = (const T *)lhs->data; const T *b = (const T *)rhs->data;
+        switch (V) {
+            case 4: gp::equal_kernel<T, 4><<<grid, threads, 0, ctx->stream>>>(a, b, total, (int *)flag.p); break;
+            case 2: gp::equal_kernel<T, 2><<<grid, threads, 0, ctx->stream>>>(a, b, total, (int *)flag.p); break;
+            default: gp::equal_kernel<T, 1><<<grid, threads, 0, ctx->stream>>>(a, b, total, (int *)flag.p); break;
+        } gp::count_launch();
+        GP_CHECK_LAUNCH("equal_kernel"); return 0;);
+    if (st) return st;
+    int diff = 0;
+    GP_CUDA(cudaMemcpyAsync(&diff, flag.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream), "cudaMemcpyAsync(equal)");
+    GP_CUDA(cudaStreamSynchronize(ctx->stream), "cudaStreamSynchronize(equal)");  // the result is a host value
+    *out_equal = diff ? 0 : 1;
+    return 0;
+}

@@ -1,0 +1,211 @@
+// MatrixDecompose.inl — gadget matrix, gadget decomposition, fused mul_decompose.
+// Replaces cuda/src/matrix/MatrixDecompose.cu (gpu_matrix_fill_gadget :307-453,
+// fill_small_decomposed_identity_chunk :507-890, gpu_matrix_decompose_base :892-1342).
+// Decomposition + forward NTT is ONE kernel (digit extraction is the load functor of the
+// NTT, ntt.cuh decompose_kernel): no memset, no coefficient-form digit matrix in HBM,
+// no separate NTT sweep.
+
+namespace {
+
+uint64_t host_powmod(uint64_t b, uint64_t e, uint64_t q) {
+    unsigned __int128 r = 1 % q, c = b % q;
+    for (; e; e >>= 1) {
+        if (e & 1) r = r * c % q;
+        c = c * c % q;
+    }
+    return (uint64_t)r;
+}
+
+template <typename T>
+int run_fill_gadget(GpuContext *ctx, GpuMatrix *out, uint32_t base_bits, bool small) {
+    const uint32_t dpt = digits_per_tower(ctx, base_bits), limbs = (uint32_t)out->limbs();
+    const uint32_t ell = small ? dpt : dpt * limbs;
+    std::vector<T> pow((size_t)limbs * dpt);
+    for (uint32_t l = 0; l < limbs; l++)
+        for (uint32_t dg = 0; dg < dpt; dg++)  // 2^(bb*dg) mod q_l (MatrixDecompose.cu:235-252)
+            pow[(size_t)l * dpt + dg] = (T)host_powmod(2, (uint64_t)base_bits * dg, ctx->moduli[l]);
+    Scratch tab;
+    if (tab.alloc(pow.size() * sizeof(T), ctx->stream)) return 1;
+    GP_CUDA(cudaMemcpyAsync(tab.p, pow.data(), pow.size() * sizeof(T), cudaMemcpyHostToDevice, ctx->stream),
+            "cudaMemcpyAsync(gadget table)");
+    const size_t words = out->polys() * out->poly_words();
+    const unsigned threads = 256, grid = stride_grid(ctx, words, threads);
+    gp::gadget_fill_kernel<T><<<grid, threads, 0, ctx->stream>>>((T *)out->data, (const T *)tab.p, words, (uint32_t)out->rows, ell,
+                                                               dpt, limbs, (uint32_t)ctx->logN, small ? 1 : 0);
+    gp::count_launch();
+    GP_CHECK_LAUNCH("gadget_fill_kernel");
+    return 0;
+}
+
+int fill_gadget_common(GpuMatrix *out, uint32_t base_bits, bool small, const char *name) {
+    if (!out || !out->ctx) return gp::set_error(std::string("invalid ") + name + " arguments");
+    if (base_bits == 0 || base_bits >= 63) return gp::set_error(std::string("invalid base_bits in ") + name);  // :316
+    if (out->level < 0) return gp::set_error(std::string("invalid level in ") + name);
+    GpuContext *ctx = out->ctx;
+    const size_t dpt = digits_per_tower(ctx, base_bits);
+    const size_t ell = small ? dpt : dpt * out->limbs();
+    if (out->cols != out->rows * ell) return gp::set_error(std::string("output size mismatch in ") + name);  // :363
+    out->format = GPU_POLY_FORMAT_EVAL;  // :431-437
+    if (out->polys() == 0) return 0;
+    if (bind_device(ctx)) return 1;
+    return GP_DISPATCH_WIDTH(ctx, return run_fill_gadget<T>(ctx, out, base_bits, small););
+}
+
+// out (rows*ell x cols) <- digits of src[:, src_col0 : src_col0 + cols] (src in COEFF form)
+template <typename T>
+int run_decompose(GpuContext *ctx, const T *src_coeff, T *out, size_t rows, size_t src_cols, size_t src_col0, size_t cols,
+                  uint32_t limbs, uint32_t base_bits, bool small, bool to_eval) {
+    const uint32_t dpt = digits_per_tower(ctx, base_bits);
+    gp::DecompGeom g;
+    g.limbs = limbs;
+    g.src_cols = (uint32_t)src_cols;
+    g.src_col0 = (uint32_t)src_col0;
+    g.cols = (uint32_t)cols;
+    g.dpt = dpt;
+    g.ell = small ? dpt : dpt * limbs;
+    g.base_bits = base_bits;
+    const size_t opl = rows * g.ell * cols * limbs;
+    if (opl == 0) return 0;
+    const int logn = ctx->logN, logb = ntt_block_log<T>(ctx), top = logn - logb;
+    const size_t smem = gp::ntt_smem_bytes<T>(logb);
+    if (ensure_ntt_smem<T>(ctx, smem)) return 1;
+    const auto *tw = (const gp::TwPair<T> *)ctx->d_fwd;
+    const auto *lc = (const gp::LimbConst<T> *)ctx->d_limb;
+    const unsigned grid = (unsigned)(opl << top), threads = gp::NttCfg<T>::kThreads;
+    if (to_eval && top == 0) {
+        gp::decompose_kernel<T, true><<<grid, threads, smem, ctx->stream>>>(src_coeff, out, g, (uint32_t)logn, (uint32_t)logb, tw, lc);
+        gp::count_launch();
+        GP_CHECK_LAUNCH("decompose_kernel");
+        return 0;
+    }
+    gp::decompose_kernel<T, false><<<grid, threads, 0, ctx->stream>>>(src_coeff, out, g, (uint32_t)logn, (uint32_t)logb, tw, lc);
+    gp::count_launch();
+    GP_CHECK_LAUNCH("decompose_kernel");
+    if (to_eval) return run_ntt_fwd<T>(ctx, out, out, rows * g.ell * cols, limbs);
+    return 0;
+}
+
+int decompose_common(const GpuMatrix *src, uint32_t base_bits, GpuMatrix *out, bool small) {
+    if (!src || !out) return gp::set_error("invalid gpu_matrix_decompose_base arguments");
+    if (base_bits == 0) return gp::set_error("base_bits must be non-zero in gpu_matrix_decompose_base");
+    if (base_bits >= 63) return gp::set_error("base_bits too large in gpu_matrix_decompose_base");
+    if (!same_ctx(src, out)) return gp::set_error("context mismatch in gpu_matrix_decompose_base");
+    if (src->level < 0) return gp::set_error("invalid level in gpu_matrix_decompose_base");
+    if (out == src || (out->data && out->data == src->data))
+        return gp::set_error("gpu_matrix_decompose_base output must not alias the input");
+    GpuContext *ctx = src->ctx;
+    const int want = out->format;  // the caller creates `out` in the format it wants back (MatrixDecompose.cu:910-914)
+    if (want != GPU_POLY_FORMAT_COEFF && want != GPU_POLY_FORMAT_EVAL)
+        return gp::set_error("invalid output format in gpu_matrix_decompose_base");
+    const size_t dpt = digits_per_tower(ctx, base_bits);
+    const size_t ell = small ? dpt : dpt * src->limbs();
+    if (out->rows != src->rows * ell || out->cols != src->cols)
+        return gp::set_error("output size mismatch in gpu_matrix_decompose_base");  // :937-946
+    if (src->polys() == 0) {
+        out->format = GPU_POLY_FORMAT_EVAL;
+        return 0;
+    }
+    if (bind_device(ctx)) return 1;
+    const uint32_t limbs = (uint32_t)src->limbs();
+    int st = GP_DISPATCH_WIDTH(
+        ctx, const T *coeff = (const T *)src->data; Scratch tmp;
+        if (src->format == GPU_POLY_FORMAT_EVAL) {  // coefficient form of the input, without touching it (:965-988)
+            if (tmp.alloc(src->bytes(), ctx->stream)) return 1;
+            if (run_ntt_inv<T>(ctx, (const T *)src->data, (T *)tmp.p, src->polys(), limbs)) return 1;
+            coeff = (const T *)tmp.p;
+        } return run_decompose<T>(ctx, coeff, (T *)out->data, src->rows, src->cols, 0, src->cols, limbs, base_bits, small,
+                                  want == GPU_POLY_FORMAT_EVAL););
+    if (!st) out->format = want;
+    return st;
+}
+}  // namespace
+
+extern "C" int gpu_matrix_fill_gadget(GpuMatrix *out, uint32_t base_bits) {
+    return fill_gadget_common(out, base_bits, false, "gpu_matrix_fill_gadget");
+}
+extern "C" int gpu_matrix_fill_small_gadget(GpuMatrix *out, uint32_t base_bits) {
+    return fill_gadget_common(out, base_bits, true, "gpu_matrix_fill_small_gadget");
+}
+extern "C" int gpu_matrix_decompose_base(const GpuMatrix *src, uint32_t base_bits, GpuMatrix *out) {
+    return decompose_common(src, base_bits, out, false);
+}
+extern "C" int gpu_matrix_decompose_base_small(const GpuMatrix *src, uint32_t base_bits, GpuMatrix *out) {
+    return decompose_common(src, base_bits, out, true);
+}
+
+extern "C" int gpu_matrix_fill_small_decomposed_identity_chunk(GpuMatrix *out, const GpuMatrix *scalar_by_digit, size_t chunk_idx) {
+    const char *fn = "gpu_matrix_fill_small_decomposed_identity_chunk";
+    if (!out || !scalar_by_digit) return gp::set_error(std::string("invalid ") + fn + " arguments");
+    if (!same_ctx(out, scalar_by_digit)) return gp::set_error(std::string("context mismatch in ") + fn);
+    if (out->rows != out->cols) return gp::set_error(std::string("output must be square in ") + fn);
+    if (scalar_by_digit->rows != 1 || scalar_by_digit->cols == 0)
+        return gp::set_error(std::string("scalar_by_digit must be 1 x chunk_count in ") + fn);
+    if (out->format != scalar_by_digit->format) return gp::set_error(std::string("format mismatch in ") + fn);
+    const size_t size = out->rows, digits = scalar_by_digit->cols;
+    if (chunk_idx >= digits) return gp::set_error(std::string("chunk_idx out of range in ") + fn);
+    if (size == 0) return 0;
+    if (out->level < 0) return gp::set_error(std::string("invalid level in ") + fn);
+    GpuContext *ctx = out->ctx;
+    if (bind_device(ctx)) return 1;
+    const size_t pw = out->poly_words();
+    return GP_DISPATCH_WIDTH(
+        ctx, const int V = vec_width<T>(ctx); const size_t total = size * size * pw / V;
+        const unsigned threads = 256, grid = stride_grid(ctx, total, threads);
+        T *d = (T *)out->data; const T *s = (const T *)scalar_by_digit->data;
+        switch (V) {
+            case 4: gp::small_identity_chunk_kernel<T, 4><<<grid, threads, 0, ctx->stream>>>(d, s, size, chunk_idx, digits, total, pw); break;
+            case 2: gp::small_identity_chunk_kernel<T, 2><<<grid, threads, 0, ctx->stream>>>(d, s, size, chunk_idx, digits, total, pw); break;
+            default: gp::small_identity_chunk_kernel<T, 1><<<grid, threads, 0, ctx->stream>>>(d, s, size, chunk_idx, digits, total, pw); break;
+        } gp::count_launch();
+        GP_CHECK_LAUNCH("small_identity_chunk_kernel"); return 0;);
+}
+
+// ---- extension: S * G^-1(other) in one call ------------------------------------------
+// Replaces the slice -> decompose_owned -> mul -> copy_block loop of
+// GpuDCRTPolyMatrix::mul_decompose (src/matrix/gpu_dcrt_poly.rs:1414-1493; ~5 matrix
+// creations and log2(n)+5 launches per column there).  Here: one INTT of `other`, then per
+// column chunk one fused digit+NTT kernel and one product kernel writing straight into the
+// output columns.  The chunk width keeps the digit block inside the 126 MB L2 so the
+// digits are produced and consumed on chip (MXX_MUL_DECOMPOSE_L2_BYTES overrides the
+// budget; the reference's knob is MXX_MUL_DECOMPOSE_COLUMN_CHUNK_WIDTH, src/env.rs:148).
+extern "C" int gpu_matrix_mul_decompose(GpuMatrix *out, const GpuMatrix *lhs, const GpuMatrix *rhs, uint32_t base_bits, int small) {
+    if (binary_check("gpu_matrix_mul_decompose", out, lhs, rhs)) return 1;
+    if (base_bits == 0 || base_bits >= 63) return gp::set_error("invalid base_bits in gpu_matrix_mul_decompose");
+    if (out->level < 0) return gp::set_error("invalid level in gpu_matrix_mul_decompose");
+    GpuContext *ctx = out->ctx;
+    const size_t dpt = digits_per_tower(ctx, base_bits);
+    const size_t ell = small ? dpt : dpt * out->limbs();
+    const size_t d = rhs->rows, c = rhs->cols, m = d * ell;
+    if (lhs->cols != m || out->rows != lhs->rows || out->cols != c)
+        return gp::set_error("size mismatch in gpu_matrix_mul_decompose");
+    if (lhs->format != GPU_POLY_FORMAT_EVAL) return gp::set_error("gpu_matrix_mul_decompose requires an EVAL left operand");
+    if (out == lhs || out == rhs || (out->data && (out->data == lhs->data || out->data == rhs->data)))
+        return gp::set_error("gpu_matrix_mul_decompose output must not alias an input");
+    out->format = GPU_POLY_FORMAT_EVAL;
+    if (out->polys() == 0) return 0;
+    if (bind_device(ctx)) return 1;
+    size_t budget = 48ull << 20;
+    if (const char *env = getenv("MXX_MUL_DECOMPOSE_L2_BYTES")) {
+        char *end = nullptr;
+        unsigned long long v = strtoull(env, &end, 10);
+        if (end && end != env && v) budget = v;
+    }
+    const uint32_t limbs = (uint32_t)out->limbs();
+    return GP_DISPATCH_WIDTH(
+        ctx, const size_t poly_bytes = out->poly_words() * sizeof(T);
+        size_t width = std::max<size_t>(1, budget / std::max<size_t>(1, m * poly_bytes)); width = std::min(width, c);
+        const T *coeff = (const T *)rhs->data; Scratch tmp; Scratch digits;
+        if (rhs->format == GPU_POLY_FORMAT_EVAL) {
+            if (tmp.alloc(rhs->bytes(), ctx->stream)) return 1;
+            if (run_ntt_inv<T>(ctx, (const T *)rhs->data, (T *)tmp.p, rhs->polys(), limbs)) return 1;
+            coeff = (const T *)tmp.p;
+        } if (digits.alloc(m * width * poly_bytes, ctx->stream)) return 1;
+        for (size_t c0 = 0; c0 < c; c0 += width) {
+            const size_t w = std::min(width, c - c0);
+            if (run_decompose<T>(ctx, coeff, (T *)digits.p, d, c, c0, w, limbs, base_bits, small != 0, true)) return 1;
+            gp::MatmulGeom g{};
+            g.rows = (uint32_t)lhs->rows; g.inner = (uint32_t)m; g.cols = (uint32_t)w; g.b_cols = (uint32_t)w; g.b_col0 = 0;
+            g.out_cols = (uint32_t)c; g.out_col0 = (uint32_t)c0; g.limbs = limbs;
+            if (run_matmul<T>(ctx, (T *)out->data, (const T *)lhs->data, (const T *)digits.p, g)) return 1;
+        } return 0;);
+}

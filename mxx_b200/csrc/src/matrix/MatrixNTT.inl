@@ -1,0 +1,148 @@
+// MatrixNTT.inl — host side of the batched negacyclic NTT / INTT.
+// Replaces gpu_matrix_ntt_all / gpu_matrix_intt_all and the host loop of
+// cuda/src/matrix/MatrixNTT.cu:402-811 (twist + bit-reverse + log2 n stage launches
+// + scale): one kernel per transform when a (poly, limb) fits a CTA's shared memory,
+// otherwise radix-2^k global passes for the top stages plus one shared-memory kernel.
+
+namespace {
+
+template <typename T> inline int ntt_block_log(const GpuContext *ctx) { return gp::ntt_block_log<T>(ctx->logN); }
+using gp::split_top;
+
+template <typename T> int ensure_ntt_smem(GpuContext *ctx, size_t bytes) {
+    // opt in to > 48 KB dynamic shared memory once per context and kernel family
+    if (bytes <= 48 * 1024 || ctx->smem_configured) return 0;
+    if ((int)bytes > ctx->max_smem_optin) return gp::set_error("NTT block does not fit shared memory on this device");
+    const int b = ctx->max_smem_optin;
+    GP_CUDA(cudaFuncSetAttribute(gp::ntt_fwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, b), "cudaFuncSetAttribute");
+    GP_CUDA(cudaFuncSetAttribute(gp::ntt_inv_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, b), "cudaFuncSetAttribute");
+    GP_CUDA(cudaFuncSetAttribute(gp::decompose_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, b), "cudaFuncSetAttribute");
+    GP_CUDA(cudaFuncSetAttribute(gp::decompose_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, b), "cudaFuncSetAttribute");
+    ctx->smem_configured = true;
+    return 0;
+}
+
+template <typename T, int LOGR>
+int launch_fwd_global(GpuContext *ctx, T *data, size_t pl, uint32_t limbs, uint32_t lspan) {
+    const size_t total = pl << (ctx->logN - LOGR);
+    const unsigned threads = 256, grid = (unsigned)((total + threads - 1) / threads);
+    gp::ntt_fwd_global_pass<T, LOGR><<<grid, threads, 0, ctx->stream>>>(data, total, limbs, (uint32_t)ctx->logN, lspan,
+                                                                         (const gp::TwPair<T> *)ctx->d_fwd,
+                                                                         (const gp::LimbConst<T> *)ctx->d_limb);
+    gp::count_launch();
+    GP_CHECK_LAUNCH("ntt_fwd_global_pass");
+    return 0;
+}
+template <typename T, int LOGR>
+int launch_inv_global(GpuContext *ctx, T *data, size_t pl, uint32_t limbs, uint32_t lt0, bool final_pass) {
+    const size_t total = pl << (ctx->logN - LOGR);
+    const unsigned threads = 256, grid = (unsigned)((total + threads - 1) / threads);
+    const auto *tw = (const gp::TwPair<T> *)ctx->d_inv;
+    const auto *lc = (const gp::LimbConst<T> *)ctx->d_limb;
+    if (final_pass)
+        gp::ntt_inv_global_pass<T, LOGR, true><<<grid, threads, 0, ctx->stream>>>(data, total, limbs, (uint32_t)ctx->logN, lt0, tw, lc);
+    else
+        gp::ntt_inv_global_pass<T, LOGR, false><<<grid, threads, 0, ctx->stream>>>(data, total, limbs, (uint32_t)ctx->logN, lt0, tw, lc);
+    gp::count_launch();
+    GP_CHECK_LAUNCH("ntt_inv_global_pass");
+    return 0;
+}
+
+template <typename T> int dispatch_fwd_global(GpuContext *ctx, T *d, size_t pl, uint32_t limbs, uint32_t lspan, int r) {
+    switch (r) {
+        case 1: return launch_fwd_global<T, 1>(ctx, d, pl, limbs, lspan);
+        case 2: return launch_fwd_global<T, 2>(ctx, d, pl, limbs, lspan);
+        case 3: return launch_fwd_global<T, 3>(ctx, d, pl, limbs, lspan);
+        default: return launch_fwd_global<T, 4>(ctx, d, pl, limbs, lspan);
+    }
+}
+template <typename T>
+int dispatch_inv_global(GpuContext *ctx, T *d, size_t pl, uint32_t limbs, uint32_t lt0, int r, bool fin) {
+    switch (r) {
+        case 1: return launch_inv_global<T, 1>(ctx, d, pl, limbs, lt0, fin);
+        case 2: return launch_inv_global<T, 2>(ctx, d, pl, limbs, lt0, fin);
+        case 3: return launch_inv_global<T, 3>(ctx, d, pl, limbs, lt0, fin);
+        default: return launch_inv_global<T, 4>(ctx, d, pl, limbs, lt0, fin);
+    }
+}
+
+// dst = NTT(src) for `polys` polynomials of `limbs` limbs each (src may equal dst)
+template <typename T> int run_ntt_fwd(GpuContext *ctx, const T *src, T *dst, size_t polys, uint32_t limbs) {
+    const size_t pl = polys * limbs;
+    if (pl == 0) return 0;
+    const int logn = ctx->logN, logb = ntt_block_log<T>(ctx), top = logn - logb;
+    const size_t smem = gp::ntt_smem_bytes<T>(logb);
+    if (ensure_ntt_smem<T>(ctx, smem)) return 1;
+    if (top > 0) {
+        if (src != dst)
+            GP_CUDA(cudaMemcpyAsync(dst, src, (pl << logn) * sizeof(T), cudaMemcpyDeviceToDevice, ctx->stream), "cudaMemcpyAsync(ntt)");
+        src = dst;
+        int passes[8], np = 0;
+        split_top(top, passes, &np);
+        uint32_t lspan = (uint32_t)logn;
+        for (int i = 0; i < np; i++) {
+            if (dispatch_fwd_global<T>(ctx, dst, pl, limbs, lspan, passes[i])) return 1;
+            lspan -= passes[i];
+        }
+    }
+    const unsigned grid = (unsigned)(pl << top);
+    gp::ntt_fwd_kernel<T><<<grid, gp::NttCfg<T>::kThreads, smem, ctx->stream>>>(
+        src, dst, limbs, (uint32_t)logn, (uint32_t)logb, (const gp::TwPair<T> *)ctx->d_fwd, (const gp::LimbConst<T> *)ctx->d_limb);
+    gp::count_launch();
+    GP_CHECK_LAUNCH("ntt_fwd_kernel");
+    return 0;
+}
+
+template <typename T> int run_ntt_inv(GpuContext *ctx, const T *src, T *dst, size_t polys, uint32_t limbs) {
+    const size_t pl = polys * limbs;
+    if (pl == 0) return 0;
+    const int logn = ctx->logN, logb = ntt_block_log<T>(ctx), top = logn - logb;
+    const size_t smem = gp::ntt_smem_bytes<T>(logb);
+    if (ensure_ntt_smem<T>(ctx, smem)) return 1;
+    const unsigned grid = (unsigned)(pl << top);
+    gp::ntt_inv_kernel<T><<<grid, gp::NttCfg<T>::kThreads, smem, ctx->stream>>>(
+        src, dst, limbs, (uint32_t)logn, (uint32_t)logb, (const gp::TwPair<T> *)ctx->d_inv, (const gp::LimbConst<T> *)ctx->d_limb);
+    gp::count_launch();
+    GP_CHECK_LAUNCH("ntt_inv_kernel");
+    if (top > 0) {
+        int passes[8], np = 0;
+        split_top(top, passes, &np);
+        uint32_t lt0 = (uint32_t)logb;
+        // smallest distances first; the radices are applied in reverse so the forward and
+        // inverse transforms use the same pass boundaries
+        for (int i = np - 1; i >= 0; i--) {
+            if (dispatch_inv_global<T>(ctx, dst, pl, limbs, lt0, passes[i], i == 0)) return 1;
+            lt0 += passes[i];
+        }
+    }
+    return 0;
+}
+
+int matrix_transform(GpuMatrix *mat, bool inverse) {
+    GpuContext *ctx = mat->ctx;
+    if (mat->polys() == 0 || mat->level < 0) {
+        mat->format = inverse ? GPU_POLY_FORMAT_COEFF : GPU_POLY_FORMAT_EVAL;
+        return 0;
+    }
+    if (bind_device(ctx)) return 1;
+    const uint32_t limbs = (uint32_t)mat->limbs();
+    int st = GP_DISPATCH_WIDTH(ctx, T *d = (T *)mat->data;
+                               return inverse ? run_ntt_inv<T>(ctx, d, d, mat->polys(), limbs)
+                                              : run_ntt_fwd<T>(ctx, d, d, mat->polys(), limbs););
+    if (st) return st;
+    mat->format = inverse ? GPU_POLY_FORMAT_COEFF : GPU_POLY_FORMAT_EVAL;
+    return 0;
+}
+}  // namespace
+
+extern "C" int gpu_matrix_ntt_all(GpuMatrix *mat) {
+    if (!mat || !mat->ctx) return gp::set_error("invalid gpu_matrix_ntt_all arguments");
+    if (mat->format == GPU_POLY_FORMAT_EVAL) return 0;  // MatrixNTT.cu:793-796
+    return matrix_transform(mat, false);
+}
+
+extern "C" int gpu_matrix_intt_all(GpuMatrix *mat) {
+    if (!mat || !mat->ctx) return gp::set_error("invalid gpu_matrix_intt_all arguments");
+    if (mat->format == GPU_POLY_FORMAT_COEFF) return 0;  // MatrixNTT.cu:806-809
+    return matrix_transform(mat, true);
+}
