@@ -1,0 +1,440 @@
+"""GpuDCRTPolyMatrix — host mirror of src/matrix/gpu_dcrt_poly.rs (the `PolyMatrix`
+surface of src/matrix/mod.rs:45-379 over the gpu_* C ABI).
+
+Same method names, argument meaning and failure behaviour as the Rust type so the parity
+tests read like the reference's own (`gpu_dcrt_poly.rs:1926-2700`).  Host-side matrices
+are numpy uint64 arrays of shape (nrow, ncol, level+1, n): the flat
+[poly row-major][limb][coeff] little-endian u64 layout of gpu_dcrt_poly.rs:769-817,
+1916-1920.  All compute happens in libgpupoly.so; nothing here touches residues.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import ffi
+from .ffi import GPU_POLY_FORMAT_COEFF, GPU_POLY_FORMAT_EVAL, check_status
+from .params import GpuDCRTPolyParams
+
+
+def mul_decompose_column_chunk_width() -> int:
+    """src/env.rs:148-154: MXX_MUL_DECOMPOSE_COLUMN_CHUNK_WIDTH, default 1."""
+    try:
+        return max(1, int(os.environ.get("MXX_MUL_DECOMPOSE_COLUMN_CHUNK_WIDTH", "1")))
+    except ValueError:
+        return 1
+
+
+class PinnedBuffer:
+    """Page-locked host buffer from gpu_pinned_alloc (gpu.rs:236-237), viewed as numpy uint64."""
+
+    def __init__(self, shape, library=None):
+        self._L = library or ffi.lib()
+        self.shape = tuple(int(s) for s in shape)
+        self.nbytes = int(np.prod(self.shape)) * 8
+        self._ptr = self._L.gpu_pinned_alloc(self.nbytes) if self.nbytes else None
+        if self.nbytes and not self._ptr:
+            check_status(1, "gpu_pinned_alloc", self._L)
+        buf = (C.c_uint64 * (self.nbytes // 8)).from_address(self._ptr) if self.nbytes else (C.c_uint64 * 0)()
+        self.array = np.frombuffer(buf, dtype=np.uint64).reshape(self.shape)
+
+    def free(self):
+        if getattr(self, "_ptr", None):
+            self.array = None
+            self._L.gpu_pinned_free(self._ptr)
+            self._ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class GpuDCRTPolyMatrix:
+    def __init__(self, params: GpuDCRTPolyParams, nrow: int, ncol: int, level: int | None = None, is_ntt: bool = True):
+        """new_empty_with_state (gpu_dcrt_poly.rs:222-256): uninitialised device storage."""
+        self.params = params
+        self._L = params._L
+        self.nrow, self.ncol = int(nrow), int(ncol)
+        self.level = params.crt_depth - 1 if level is None else int(level)
+        assert self.level < params.crt_depth, "invalid level for matrix create"
+        self.is_ntt = bool(is_ntt)
+        h = C.c_void_p()
+        fmt = GPU_POLY_FORMAT_EVAL if is_ntt else GPU_POLY_FORMAT_COEFF
+        check_status(self._L.gpu_matrix_create(params.ctx_raw(), self.level, self.nrow, self.ncol, fmt, C.byref(h)),
+                     "gpu_matrix_create", self._L)
+        self.raw = h
+
+    # -- lifetime ---------------------------------------------------------------------
+    def destroy(self):
+        if getattr(self, "raw", None):
+            self._L.gpu_matrix_destroy(self.raw)
+            self.raw = None
+
+    def __del__(self):  # Drop, gpu_dcrt_poly.rs:145-152
+        try:
+            self.destroy()
+        except Exception:
+            pass
+
+    # -- constructors -------------------------------------------------------------------
+    @classmethod
+    def new_empty(cls, params, nrow, ncol):
+        return cls(params, nrow, ncol)
+
+    @classmethod
+    def zero(cls, params, nrow, ncol, level=None, is_ntt=True):
+        """new_zero_with_state (gpu_dcrt_poly.rs:344-365): load an all-zero host buffer."""
+        out = cls(params, nrow, ncol, level, is_ntt)
+        if nrow and ncol:
+            host = np.zeros((nrow, ncol, out.level + 1, params.ring_dimension), dtype=np.uint64)
+            out.load_rns(host, out._fmt())
+        return out
+
+    @classmethod
+    def from_rns(cls, params, host: np.ndarray, is_ntt: bool = True):
+        """from_cpu_matrix / from_rns_snapshot (gpu_dcrt_poly.rs:769-817, 681-698): host residues -> device."""
+        host = np.ascontiguousarray(host, dtype=np.uint64)
+        assert host.ndim == 4 and host.shape[3] == params.ring_dimension
+        out = cls(params, host.shape[0], host.shape[1], host.shape[2] - 1, is_ntt)
+        out.load_rns(host, out._fmt())
+        return out
+
+    @classmethod
+    def identity(cls, params, size, scalar: "GpuDCRTPolyMatrix | None" = None):
+        """gpu_dcrt_poly.rs:1158-1188: size x size, `scalar` (a 1x1 matrix, default 1) on the diagonal."""
+        n, L = params.ring_dimension, params.crt_depth
+        host = np.zeros((size, size, L, n), dtype=np.uint64)
+        if scalar is None:
+            diag = np.ones((L, n), dtype=np.uint64)  # the constant 1 evaluates to 1 at every slot
+        else:
+            s = scalar.clone()
+            s.ntt_in_place()
+            diag = s.to_rns()[0, 0]
+        for i in range(size):
+            host[i, i] = diag
+        return cls.from_rns(params, host, True)
+
+    @classmethod
+    def gadget_matrix(cls, params, size):
+        """gpu_dcrt_poly.rs:1254-1263"""
+        if size == 0:
+            return cls(params, 0, 0)
+        out = cls(params, size, size * params.modulus_digits())
+        check_status(out._L.gpu_matrix_fill_gadget(out.raw, params.base_bits), "gpu_matrix_fill_gadget", out._L)
+        out.is_ntt = True
+        return out
+
+    @classmethod
+    def small_gadget_matrix(cls, params, size):
+        """gpu_dcrt_poly.rs:1265-1274"""
+        if size == 0:
+            return cls(params, 0, 0)
+        out = cls(params, size, size * params.digits_per_tower)
+        check_status(out._L.gpu_matrix_fill_small_gadget(out.raw, params.base_bits), "gpu_matrix_fill_small_gadget", out._L)
+        out.is_ntt = True
+        return out
+
+    @classmethod
+    def small_decomposed_identity_chunk(cls, params, size, chunk_idx, chunk_count, scalar_by_digit: "GpuDCRTPolyMatrix"):
+        """gpu_dcrt_poly.rs:1296-1326; scalar_by_digit is the 1 x chunk_count row of digit polynomials."""
+        assert chunk_count > 0 and scalar_by_digit.size() == (1, chunk_count)
+        if size == 0:
+            return cls(params, 0, 0)
+        out = cls(params, size, size, scalar_by_digit.level, scalar_by_digit.is_ntt)
+        check_status(out._L.gpu_matrix_fill_small_decomposed_identity_chunk(out.raw, scalar_by_digit.raw, chunk_idx),
+                     "gpu_matrix_fill_small_decomposed_identity_chunk", out._L)
+        return out
+
+    # -- host <-> device ------------------------------------------------------------------
+    def _fmt(self):
+        return GPU_POLY_FORMAT_EVAL if self.is_ntt else GPU_POLY_FORMAT_COEFF
+
+    def _wait(self, events, what):
+        if events:  # gpu_dcrt_poly.rs:591-595
+            st = self._L.gpu_event_set_wait(events)
+            self._L.gpu_event_set_destroy(events)
+            check_status(st, "gpu_event_set_wait", self._L)
+
+    def bytes_per_poly(self) -> int:
+        return (self.level + 1) * self.params.ring_dimension * 8  # gpu_dcrt_poly.rs:1916-1920
+
+    def load_rns(self, host: np.ndarray, fmt: int, wait: bool = True):
+        """load_rns_bytes (gpu_dcrt_poly.rs:629-663)."""
+        assert host.dtype == np.uint64 and host.flags["C_CONTIGUOUS"]
+        if host.size == 0:
+            return None
+        assert host.size * 8 == self.nrow * self.ncol * self.bytes_per_poly()
+        ev = C.c_void_p()
+        check_status(self._L.gpu_matrix_load_rns_batch(self.raw, host.ctypes.data, self.bytes_per_poly(), fmt, C.byref(ev)),
+                     "gpu_matrix_load_rns_batch", self._L)
+        self.is_ntt = fmt == GPU_POLY_FORMAT_EVAL
+        if wait:
+            self._wait(ev, "load")
+            return None
+        return ev
+
+    def store_rns(self, out: np.ndarray, fmt: int | None = None, wait: bool = True):
+        """store_rns_bytes (gpu_dcrt_poly.rs:576-596): the tag must equal the current domain."""
+        assert out.dtype == np.uint64 and out.flags["C_CONTIGUOUS"]
+        if out.size == 0:
+            return None
+        ev = C.c_void_p()
+        check_status(self._L.gpu_matrix_store_rns_batch(self.raw, out.ctypes.data, self.bytes_per_poly(),
+                                                        self._fmt() if fmt is None else fmt, C.byref(ev)),
+                     "gpu_matrix_store_rns_batch", self._L)
+        if wait:
+            self._wait(ev, "store")
+            return None
+        return ev
+
+    def to_rns(self) -> np.ndarray:
+        """to_rns_snapshot (gpu_dcrt_poly.rs:665-679): residues in the matrix's current domain."""
+        out = np.empty((self.nrow, self.ncol, self.level + 1, self.params.ring_dimension), dtype=np.uint64)
+        self.store_rns(out)
+        return out
+
+    def store_const_coeff_words(self) -> np.ndarray:
+        """gpu_dcrt_poly.rs:598-627: coefficient 0 of every limb; requires the coefficient domain."""
+        words = np.zeros((self.nrow, self.ncol, self.level + 1), dtype=np.uint64)
+        if words.size == 0:
+            return words
+        ev = C.c_void_p()
+        check_status(self._L.gpu_matrix_store_const_coeff_batch(self.raw, words.ctypes.data_as(ffi.u64p), self.level + 1, C.byref(ev)),
+                     "gpu_matrix_store_const_coeff_batch", self._L)
+        self._wait(ev, "store_const")
+        return words
+
+    # -- shape / domain --------------------------------------------------------------------
+    def size(self):
+        return (self.nrow, self.ncol)
+
+    def clone(self):
+        out = GpuDCRTPolyMatrix(self.params, self.nrow, self.ncol, self.level, self.is_ntt)
+        check_status(self._L.gpu_matrix_copy(out.raw, self.raw), "gpu_matrix_copy", self._L)
+        return out
+
+    def ntt_in_place(self):
+        check_status(self._L.gpu_matrix_ntt_all(self.raw), "gpu_matrix_ntt_all", self._L)
+        self.is_ntt = True
+
+    def intt_all_in_place(self):  # gpu_dcrt_poly.rs:295-302
+        check_status(self._L.gpu_matrix_intt_all(self.raw), "gpu_matrix_intt_all", self._L)
+        self.is_ntt = False
+
+    def into_coeff_domain(self):
+        self.intt_all_in_place()
+        return self
+
+    def __eq__(self, other):  # PartialEq, gpu_dcrt_poly.rs:199-217
+        if not isinstance(other, GpuDCRTPolyMatrix):
+            return NotImplemented
+        if (self.params is not other.params and self.params.moduli != other.params.moduli) or self.size() != other.size() \
+                or self.level != other.level or self.is_ntt != other.is_ntt:
+            return False
+        if self.raw.value == other.raw.value:
+            return True
+        eq = C.c_int(0)
+        check_status(self._L.gpu_matrix_equal(self.raw, other.raw, C.byref(eq)), "gpu_matrix_equal", self._L)
+        return eq.value != 0
+
+    __hash__ = None
+
+    # -- blocks -------------------------------------------------------------------------------
+    def copy_block_from(self, src, dst_row, dst_col, src_row, src_col, rows, cols):  # gpu_dcrt_poly.rs:372-389
+        check_status(self._L.gpu_matrix_copy_block(self.raw, src.raw, dst_row, dst_col, src_row, src_col, rows, cols),
+                     "gpu_matrix_copy_block", self._L)
+        self.is_ntt = src.is_ntt
+
+    def add_block_from(self, src, dst_row, dst_col, src_row, src_col, rows, cols):  # gpu_dcrt_poly.rs:411-432
+        assert self.is_ntt == src.is_ntt, "add_block_from requires matching domains"
+        check_status(self._L.gpu_matrix_add_block(self.raw, src.raw, dst_row, dst_col, src_row, src_col, rows, cols),
+                     "gpu_matrix_add_block", self._L)
+
+    def slice(self, row_start, row_end, col_start, col_end):  # gpu_dcrt_poly.rs:1146-1152
+        out = GpuDCRTPolyMatrix(self.params, row_end - row_start, col_end - col_start, self.level, self.is_ntt)
+        out.copy_block_from(self, 0, 0, row_start, col_start, row_end - row_start, col_end - col_start)
+        return out
+
+    def slice_rows(self, start, end):
+        return self.slice(start, end, 0, self.ncol)
+
+    def slice_columns(self, start, end):
+        return self.slice(0, self.nrow, start, end)
+
+    def entry(self, i, j):
+        """1x1 matrix holding entry (i, j) — the GpuDCRTPoly of gpu.rs:707 is a 1x1 matrix wrapper."""
+        return self.slice(i, i + 1, j, j + 1)
+
+    def set_entry(self, i, j, elem):
+        assert elem.size() == (1, 1)
+        e = elem
+        if e.is_ntt != self.is_ntt:
+            e = elem.clone()
+            e.ntt_in_place() if self.is_ntt else e.intt_all_in_place()
+        self.copy_block_from(e, i, j, 0, 0, 1, 1)
+
+    def transpose(self):  # gpu_dcrt_poly.rs:1190-1199
+        out = GpuDCRTPolyMatrix(self.params, self.ncol, self.nrow, self.level, self.is_ntt)
+        for i in range(self.nrow):
+            for j in range(self.ncol):
+                out.copy_block_from(self, j, i, i, j, 1, 1)
+        return out
+
+    def _same_domain(self, others):
+        for o in others:
+            assert o.level == self.level and o.is_ntt == self.is_ntt, "concat requires same level and domain"
+
+    def concat_columns(self, others):  # gpu_dcrt_poly.rs:853-885
+        self._same_domain(others)
+        assert all(o.nrow == self.nrow for o in others)
+        out = GpuDCRTPolyMatrix(self.params, self.nrow, self.ncol + sum(o.ncol for o in others), self.level, self.is_ntt)
+        c = 0
+        for m in [self, *others]:
+            out.copy_block_from(m, 0, c, 0, 0, m.nrow, m.ncol)
+            c += m.ncol
+        return out
+
+    def concat_rows(self, others):  # gpu_dcrt_poly.rs:819-851
+        self._same_domain(others)
+        assert all(o.ncol == self.ncol for o in others)
+        out = GpuDCRTPolyMatrix(self.params, self.nrow + sum(o.nrow for o in others), self.ncol, self.level, self.is_ntt)
+        r = 0
+        for m in [self, *others]:
+            out.copy_block_from(m, r, 0, 0, 0, m.nrow, m.ncol)
+            r += m.nrow
+        return out
+
+    def concat_diag(self, others):  # gpu_dcrt_poly.rs:887-916
+        self._same_domain(others)
+        mats = [self, *others]
+        out = GpuDCRTPolyMatrix.zero(self.params, sum(m.nrow for m in mats), sum(m.ncol for m in mats), self.level, self.is_ntt)
+        r = c = 0
+        for m in mats:
+            out.copy_block_from(m, r, c, 0, 0, m.nrow, m.ncol)
+            r += m.nrow
+            c += m.ncol
+        return out
+
+    # -- ring operations --------------------------------------------------------------------------
+    def _binary(self, rhs, fn, name):
+        assert self.size() == rhs.size(), f"{name} requires equal shapes"
+        assert self.is_ntt == rhs.is_ntt, f"{name} requires matching domains"
+        out = GpuDCRTPolyMatrix(self.params, self.nrow, self.ncol, self.level, self.is_ntt)
+        check_status(fn(out.raw, self.raw, rhs.raw), name, self._L)
+        return out
+
+    def __add__(self, rhs):  # gpu_dcrt_poly.rs:1716-1741
+        return self._binary(rhs, self._L.gpu_matrix_add, "gpu_matrix_add")
+
+    def __sub__(self, rhs):  # gpu_dcrt_poly.rs:1744-1768
+        return self._binary(rhs, self._L.gpu_matrix_sub, "gpu_matrix_sub")
+
+    def __neg__(self):  # gpu_dcrt_poly.rs:1885-1899: zero - self
+        return GpuDCRTPolyMatrix.zero(self.params, self.nrow, self.ncol, self.level, self.is_ntt) - self
+
+    def add_in_place(self, rhs):  # gpu_dcrt_poly.rs:391-409
+        assert self.size() == rhs.size() and self.is_ntt == rhs.is_ntt
+        check_status(self._L.gpu_matrix_add(self.raw, self.raw, rhs.raw), "gpu_matrix_add", self._L)
+
+    def _eval(self):
+        """operand in the evaluation domain (a converted copy if needed; the original is not modified)"""
+        if self.is_ntt:
+            return self
+        c = self.clone()
+        c.ntt_in_place()
+        return c
+
+    def mul_scalar(self, scalar):  # gpu_dcrt_poly.rs:1770-1790 (scalar: a 1x1 matrix)
+        assert scalar.size() == (1, 1)
+        lhs, s = self._eval(), scalar._eval()
+        out = GpuDCRTPolyMatrix(self.params, self.nrow, self.ncol, self.level, True)
+        check_status(self._L.gpu_matrix_mul_scalar(out.raw, lhs.raw, s.raw), "gpu_matrix_mul_scalar", self._L)
+        return out
+
+    def __mul__(self, rhs):  # mul_internal, gpu_dcrt_poly.rs:1792-1815; Mul<P> :1853-1883
+        if rhs.size() == (1, 1) and self.ncol != 1:
+            return self.mul_scalar(rhs)
+        assert self.ncol == rhs.nrow, "matrix product requires lhs.ncol == rhs.nrow"
+        lhs, r = self._eval(), rhs._eval()
+        out = GpuDCRTPolyMatrix(self.params, self.nrow, rhs.ncol, self.level, True)
+        check_status(self._L.gpu_matrix_mul(out.raw, lhs.raw, r.raw), "gpu_matrix_mul", self._L)
+        return out
+
+    __matmul__ = __mul__
+
+    def tensor(self, other):  # gpu_dcrt_poly.rs:1225-1252
+        out = GpuDCRTPolyMatrix(self.params, self.nrow * other.nrow, self.ncol * other.ncol, self.level, True)
+        for i in range(self.nrow):
+            for j in range(self.ncol):
+                block = other.mul_scalar(self.entry(i, j))
+                out.copy_block_from(block, i * other.nrow, j * other.ncol, 0, 0, other.nrow, other.ncol)
+        return out
+
+    # -- gadget decomposition ------------------------------------------------------------------------
+    def _decompose(self, small: bool):
+        """decompose_from_raw (gpu_dcrt_poly.rs:309-328): the result comes back in the evaluation domain."""
+        p = self.params
+        ell = p.digits_per_tower if small else p.digits_per_tower * (self.level + 1)
+        out = GpuDCRTPolyMatrix(p, self.nrow * ell, self.ncol, self.level, True)
+        fn = self._L.gpu_matrix_decompose_base_small if small else self._L.gpu_matrix_decompose_base
+        check_status(fn(self.raw, p.base_bits, out.raw), "gpu_matrix_decompose_base", self._L)
+        return out
+
+    def decompose(self):  # gpu_dcrt_poly.rs:1276-1284
+        return self._decompose(False)
+
+    def small_decompose(self):  # gpu_dcrt_poly.rs:1286-1294
+        return self._decompose(True)
+
+    def get_column_matrix_decompose(self, j):  # gpu_dcrt_poly.rs:1576-1579
+        return self.slice(0, self.nrow, j, j + 1).decompose()
+
+    def mul_decompose(self, other, fused: bool | None = None, small: bool = False):
+        """S * G^-1(other) (gpu_dcrt_poly.rs:1414-1493; small: :1495-1574).
+
+        fused=False replays the reference's call sequence verbatim (column chunks of
+        MXX_MUL_DECOMPOSE_COLUMN_CHUNK_WIDTH: slice -> decompose -> mul -> copy_block), which is
+        what the unchanged Rust side issues.  fused=True (default when the library exports it) is the
+        single-call extension gpu_matrix_mul_decompose a maintainer would switch that loop to.
+        """
+        p = self.params
+        ell = p.digits_per_tower if small else p.modulus_digits()
+        assert self.ncol == other.nrow * ell, "mul_decompose requires self.ncol == other.nrow * log_base_q"
+        ncol = other.ncol
+        if self.nrow == 0 or ncol == 0:
+            return GpuDCRTPolyMatrix(p, self.nrow, ncol)
+        if fused is None:
+            fused = hasattr(self._L, "gpu_matrix_mul_decompose")
+        lhs = self._eval()
+        out = GpuDCRTPolyMatrix(p, self.nrow, ncol, self.level, True)
+        if fused:
+            check_status(self._L.gpu_matrix_mul_decompose(out.raw, lhs.raw, other.raw, p.base_bits, int(small)),
+                         "gpu_matrix_mul_decompose", self._L)
+            return out
+        width = max(1, min(mul_decompose_column_chunk_width(), ncol))
+        for c0 in range(0, ncol, width):
+            c1 = min(c0 + width, ncol)
+            col = other.slice(0, other.nrow, c0, c1)
+            dec = col._decompose(small)
+            prod = lhs * dec
+            out.copy_block_from(prod, 0, c0, 0, 0, self.nrow, c1 - c0)
+        return out
+
+    def mul_decompose_small(self, other, fused: bool | None = None):
+        return self.mul_decompose(other, fused=fused, small=True)
+
+    def mul_tensor_identity(self, other, identity_size):  # gpu_dcrt_poly.rs:1374-1390
+        w = other.nrow
+        assert self.ncol == w * identity_size
+        parts = [self.slice(0, self.nrow, i * w, (i + 1) * w) * other for i in range(identity_size)]
+        return parts[0].concat_columns(parts[1:])
+
+    def mul_tensor_identity_decompose(self, other, identity_size):  # gpu_dcrt_poly.rs:1392-1412
+        w = other.nrow * self.params.modulus_digits()
+        assert self.ncol == w * identity_size
+        parts = [self.slice(0, self.nrow, i * w, (i + 1) * w).mul_decompose(other) for i in range(identity_size)]
+        return parts[0].concat_columns(parts[1:])

@@ -1,0 +1,189 @@
+"""CPU checks of the CUDA block-level templates through the host emulation harness.
+
+mxx_b200/libgpupoly_emu.so compiles the very templates the kernels are made of
+(csrc/include/{ntt,arith}.cuh) as one-thread blocks and drives them with the launcher's
+pass schedule.  Compared here, bit for bit, with the oracle.  This validates index math,
+twiddle addressing, lazy-reduction bounds and the decompose/matmul geometry without a
+GPU; the `-m gpu` tests then check the real kernels through the C ABI.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oracle as orc
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EMU = os.path.join(ROOT, "mxx_b200", "libgpupoly_emu.so")
+u64p = C.POINTER(C.c_uint64)
+
+
+@pytest.fixture(scope="module")
+def emu():
+    if not os.path.exists(EMU):
+        import __graft_entry__ as ge
+
+        ge.build()
+    lib = C.CDLL(EMU)
+    lib.emu_ntt.argtypes = [C.c_int, C.c_int, C.c_uint32, u64p, u64p, C.c_size_t, C.c_int, C.c_int]
+    lib.emu_decompose.argtypes = [C.c_int, C.c_int, C.c_uint32, u64p, u64p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t,
+                                  C.c_uint32, C.c_int, C.c_int, u64p, C.c_int]
+    lib.emu_matmul.argtypes = [C.c_int, C.c_int, C.c_uint32, u64p, u64p, u64p, u64p] + [C.c_uint32] * 8 + [C.c_int]
+    return lib
+
+
+def p(a):
+    assert a.dtype == np.uint64 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(u64p)
+
+
+def bitrev_perm(n):
+    bits = n.bit_length() - 1
+    idx = np.arange(n)
+    out = np.zeros(n, dtype=np.int64)
+    for b in range(bits):
+        out |= ((idx >> b) & 1) << (bits - 1 - b)
+    return out
+
+
+def to_dev(eval_nat):
+    """natural-order EVAL (boundary layout) -> device order (slot s holds X[bitrev(s)])"""
+    n = eval_nat.shape[-1]
+    return np.ascontiguousarray(eval_nat[..., bitrev_perm(n)])
+
+
+def plan(n, depth, bits):
+    return orc.Plan(n, orc.prime_chain(n, bits, depth))
+
+
+CASES = [
+    # (n, depth, bits, logb_cap, force_wide)
+    (4, 2, 17, 0, 0),
+    (8, 1, 20, 0, 0),
+    (64, 3, 24, 0, 0),
+    (1024, 2, 28, 0, 0),
+    (4096, 2, 29, 0, 0),
+    (2048, 2, 51, 0, 0),
+    (256, 2, 61, 0, 0),
+    (1024, 2, 24, 0, 1),
+    # blocks smaller than the transform: exercises the global top passes
+    (1024, 2, 28, 6, 0),
+    (1024, 1, 28, 5, 0),
+    (2048, 1, 28, 3, 0),
+    (4096, 2, 51, 7, 0),
+    (512, 1, 51, 8, 0),
+    (256, 1, 24, 1, 0),
+]
+
+
+@pytest.mark.parametrize("n,depth,bits,cap,fw", CASES)
+def test_emu_ntt_matches_oracle(emu, n, depth, bits, cap, fw):
+    pl = plan(n, depth, bits)
+    mod = np.array(pl.moduli, dtype=np.uint64)
+    a = pl.uniform(1, 3, seed=11 + n)
+    want = to_dev(pl.ntt(a))
+    d = a.copy()
+    assert emu.emu_ntt(fw, n.bit_length() - 1, depth, p(mod), p(d), 3, 0, cap) == 0
+    assert np.array_equal(d, want)
+    # inverse of the device-order EVAL data gives back the coefficients
+    assert emu.emu_ntt(fw, n.bit_length() - 1, depth, p(mod), p(d), 3, 1, cap) == 0
+    assert np.array_equal(d, a)
+
+
+def test_emu_ntt_extreme_values(emu):
+    """all coefficients q-1 (largest lazy values) and all zero"""
+    for n, depth, bits in [(4096, 2, 29), (1024, 2, 61), (1024, 2, 51)]:
+        pl = plan(n, depth, bits)
+        mod = np.array(pl.moduli, dtype=np.uint64)
+        a = np.empty((1, 2, depth, n), dtype=np.uint64)
+        a[0, 0] = (mod - 1)[:, None]
+        a[0, 1] = 0
+        want = to_dev(pl.ntt(a))
+        d = a.copy()
+        assert emu.emu_ntt(0, n.bit_length() - 1, depth, p(mod), p(d), 2, 0, 0) == 0
+        assert np.array_equal(d, want)
+        e = to_dev(a)  # treat the same values as EVAL data
+        want_c = pl.intt(a)
+        assert emu.emu_ntt(0, n.bit_length() - 1, depth, p(mod), p(e), 2, 1, 0) == 0
+        assert np.array_equal(e, want_c)
+
+
+DEC_CASES = [
+    # (n, depth, bits, bb, small, cap)
+    (4, 2, 17, 1, 0, 0),
+    (4, 2, 17, 3, 0, 0),
+    (4, 1, 52, 17, 0, 0),  # unaligned last digit (src/matrix/dcrt_poly.rs:683-728)
+    (128, 2, 17, 1, 0, 0),
+    (256, 3, 24, 12, 0, 0),
+    (256, 2, 51, 17, 0, 0),
+    (256, 3, 24, 12, 1, 0),
+    (512, 2, 28, 14, 0, 5),
+    (64, 2, 51, 20, 1, 0),
+]
+
+
+@pytest.mark.parametrize("n,depth,bits,bb,small,cap", DEC_CASES)
+@pytest.mark.parametrize("to_eval", [0, 1])
+def test_emu_decompose_matches_oracle(emu, n, depth, bits, bb, small, cap, to_eval):
+    pl = plan(n, depth, bits)
+    mod = np.array(pl.moduli, dtype=np.uint64)
+    rows, cols = 2, 3
+    src = pl.uniform(rows, cols, seed=5)
+    full = pl.decompose(src, bb, bool(small))
+    if to_eval:
+        full = to_dev(pl.ntt(full))
+    ell = pl.ell(bb, bool(small))
+    # whole matrix, then a column chunk [1,3)
+    for c0, w in [(0, cols), (1, 2)]:
+        out = np.zeros((rows * ell, w, depth, n), dtype=np.uint64)
+        st = emu.emu_decompose(0, n.bit_length() - 1, depth, p(mod), p(src), rows, cols, c0, w, bb, small, to_eval, p(out), cap)
+        assert st == 0
+        assert np.array_equal(out, np.ascontiguousarray(full[:, c0:c0 + w]))
+
+
+MM_CASES = [
+    # (n, depth, bits, r, k, c, variant, fold)
+    (16, 2, 24, 1, 5, 7, 0, 0),
+    (16, 2, 29, 1, 30, 6, 0, 0),
+    (16, 2, 29, 3, 9, 5, 1, 0),
+    (16, 2, 29, 5, 9, 6, 2, 0),
+    (16, 2, 29, 2, 40, 3, 0, 3),   # forced early folds
+    (16, 2, 51, 1, 5, 7, 0, 0),
+    (16, 2, 61, 3, 21, 5, 1, 0),   # 61-bit: 16 products per 128-bit accumulator
+    (16, 2, 61, 5, 9, 6, 2, 2),
+    (2, 1, 20, 2, 3, 2, 3, 0),     # ring smaller than a vector: scalar variant
+    (4, 2, 17, 2, 3, 2, 3, 0),
+]
+
+
+@pytest.mark.parametrize("n,depth,bits,r,k,c,variant,fold", MM_CASES)
+def test_emu_matmul_matches_oracle(emu, n, depth, bits, r, k, c, variant, fold):
+    pl = plan(n, depth, bits)
+    mod = np.array(pl.moduli, dtype=np.uint64)
+    A = pl.uniform(r, k, seed=1)
+    B = pl.uniform(k, c, seed=2)
+    want = pl.mul(A, B)
+    out = np.zeros_like(want)
+    assert emu.emu_matmul(0, n.bit_length() - 1, depth, p(mod), p(out), p(A), p(B), r, k, c, c, 0, c, 0, fold, variant) == 0
+    assert np.array_equal(out, want)
+    # a column window of B into a column window of a wider output
+    if c >= 3:
+        wide = np.full((r, c + 2, depth, n), 7, dtype=np.uint64)
+        assert emu.emu_matmul(0, n.bit_length() - 1, depth, p(mod), p(wide), p(A), p(B), r, k, c - 1, c, 1, c + 2, 2, fold, variant) == 0
+        assert np.array_equal(wide[:, 2:c + 1], want[:, 1:])
+        assert np.all(wide[:, :2] == 7) and np.all(wide[:, c + 1:] == 7)
+
+
+def test_emu_matmul_worst_case_accumulation(emu):
+    """every operand q-1: the largest lazily accumulated sums"""
+    for bits, n in [(29, 16), (61, 16), (24, 16)]:
+        pl = plan(n, 1, bits)
+        mod = np.array(pl.moduli, dtype=np.uint64)
+        k = 70
+        A = np.full((1, k, 1, n), pl.moduli[0] - 1, dtype=np.uint64)
+        B = np.full((k, 4, 1, n), pl.moduli[0] - 1, dtype=np.uint64)
+        want = pl.mul(A, B)
+        out = np.zeros_like(want)
+        assert emu.emu_matmul(0, n.bit_length() - 1, 1, p(mod), p(out), p(A), p(B), 1, k, 4, 4, 0, 4, 0, 0, 0) == 0
+        assert np.array_equal(out, want)
