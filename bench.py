@@ -1,0 +1,435 @@
+#!/usr/bin/env python
+"""bench.py — DCRT matrix-muls/s (and NTT Gcoeff/s, mul_decompose/s) on N B200s.
+
+Contract: `python bench.py --gpus N --steps K --warmup W` prints ONE JSON line on rank 0.
+
+Primary workload (config.workload = "C1-R"): the reference's own bench_matrix_mul shape
+(benches/bench_matrix_mul_{cpu,gpu}.rs:10-16): DCRTPolyMatrix 1x30 * 30x120, n = 2^14,
+15 CRT limbs of 24 bits, operands in the evaluation domain, uniformly random residues.
+One "step" = one such matrix product.  At N > 1 every rank multiplies its own operand pair
+(independent products, no data-path collective: scaling = "weak").
+
+  value     matrix-muls/s with the operands resident in HBM (CUDA events on the context stream)
+  e2e       the same metric through the reference-facing C ABI with HOST buffers: per step
+            gpu_matrix_load_rns_batch(A), (B) from pinned memory -> gpu_matrix_mul ->
+            gpu_matrix_store_rns_batch(result) -> gpu_event_set_wait
+  roofline  matmul_kernel against the measured HBM copy bandwidth (MEASURED_PEAKS.json)
+  ntt / mul_decompose   the other two kernels of the path, each with its own roofline
+  cpu_baseline          the oracle port (C + OpenMP) of the reference CPU loop on the host cores
+
+`--impl reference` times the reference's CPU algorithm for the same workload (oracle port:
+OpenFHE and cargo are absent here) with all host threads.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+# ---- workload definitions ---------------------------------------------
+C1R = dict(name="C1-R", n=1 << 14, depth=15, bits=24, bb=12, r=1, k=30, c=120)
+C3A = dict(name="C3-a", n=1 << 14, depth=15, bits=24, bb=12, r=1, d=1, c=30)
+NTT_CASES = [  # (n, depth, bits): ~256 MiB of device residues per batch (> the 126 MB L2)
+    (1 << 14, 16, 28), (1 << 15, 8, 28), (1 << 16, 8, 28),
+    (1 << 14, 8, 51), (1 << 15, 8, 51), (1 << 16, 4, 51),
+]
+NTT_BATCH_BYTES = 256 << 20
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def uniform_host(out: np.ndarray, moduli, seed: int, threads: int = 8) -> None:
+    """out[(polys), limb, n] <- uniform residues in [0, q_limb); threaded numpy PCG64 streams."""
+    flat = out.reshape(-1, len(moduli), out.shape[-1])
+    polys = flat.shape[0]
+    chunks = [(i, min(i + max(1, polys // (threads * 4)), polys)) for i in range(0, polys, max(1, polys // (threads * 4)))]
+    seeds = np.random.SeedSequence(seed).spawn(len(chunks))
+
+    def work(arg):
+        (lo, hi), ss = arg
+        rng = np.random.Generator(np.random.PCG64(ss))
+        for l, q in enumerate(moduli):
+            flat[lo:hi, l, :] = rng.integers(0, q, size=(hi - lo, flat.shape[-1]), dtype=np.uint64)
+
+    from concurrent.futures import ThreadPoolExecutor
+
+    with ThreadPoolExecutor(threads) as ex:
+        list(ex.map(work, zip(chunks, seeds)))
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device: int):
+        self.device, self.rows, self.proc = device, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.device)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(names, r[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---- distributed plumbing (one process per GPU; NCCL only for the barrier / max-over-ranks) ---
+class Dist:
+    def __init__(self, n_gpus: int):
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        self.torch = None
+        if self.world > 1:
+            import torch
+            import torch.distributed as dist
+
+            self.torch, self.dist = torch, dist
+            torch.cuda.set_device(self.local_rank)
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local_rank))
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+            self.torch.cuda.synchronize()
+
+    def max(self, x: float) -> float:
+        if self.world == 1:
+            return x
+        t = self.torch.tensor([x], dtype=self.torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def close(self):
+        if self.world > 1:
+            self.dist.destroy_process_group()
+
+
+class LocalDist:
+    world, rank = 1, 0
+
+    def barrier(self):
+        pass
+
+    def max(self, x):
+        return x
+
+
+def timed(params, dist, fn, steps: int, warmup: int):
+    """W untimed + exactly K timed calls of fn, CUDA events on the context stream, barrier +
+    synchronize on both sides, max over ranks.  Returns total ms for the K steps."""
+    for _ in range(warmup):
+        fn()
+    params.synchronize()
+    dist.barrier()
+    t = params.timer()
+    t.start()
+    for _ in range(steps):
+        fn()
+    t.stop()
+    ms = t.elapsed_ms()
+    params.synchronize()
+    dist.barrier()
+    return dist.max(ms)
+
+
+def make_params(cfg, device):
+    from mxx_b200 import GpuDCRTPolyParams, standard_moduli
+
+    moduli = standard_moduli(cfg["n"], cfg["depth"], cfg["bits"])
+    return GpuDCRTPolyParams(cfg["n"], moduli, cfg.get("bb", 12), gpu_ids=(device,)), moduli
+
+
+def bench_ntt(device, steps, warmup, hbm_peak):
+    """configs[1]: batched NTT -> INTT round trips; Gcoeff/s per direction against the HBM roofline."""
+    from mxx_b200 import GpuDCRTPolyMatrix, ffi
+
+    out = []
+    for n, depth, bits in NTT_CASES:
+        cfg = dict(n=n, depth=depth, bits=bits, bb=14)
+        params, moduli = make_params(cfg, device)
+        W = 4 if max(moduli) < (1 << 30) else 8
+        P = max(1, NTT_BATCH_BYTES // (W * depth * n))
+        host = np.empty((1, P, depth, n), dtype=np.uint64)
+        uniform_host(host, moduli, seed=0x6D7878_0002)
+        m = GpuDCRTPolyMatrix.from_rns(params, host, is_ntt=False)
+        L = ffi.lib()
+
+        def step():
+            ffi.check_status(L.gpu_matrix_ntt_all(m.raw), "gpu_matrix_ntt_all")
+            m.is_ntt = True
+            ffi.check_status(L.gpu_matrix_intt_all(m.raw), "gpu_matrix_intt_all")
+            m.is_ntt = False
+
+        for _ in range(warmup):
+            step()
+        params.synchronize()
+        t = params.timer()
+        t.start()
+        for _ in range(steps):
+            step()
+        t.stop()
+        ms = t.elapsed_ms() / steps
+        coeffs = P * depth * n
+        algo_bytes = 2 * (2 * W * coeffs)  # one read + one write per coefficient, two directions
+        gbs = algo_bytes / (ms * 1e-3) / 1e9
+        out.append({"n": n, "limbs": depth, "crt_bits": bits, "word_bytes": W, "polys": P, "ms_roundtrip": round(ms, 4),
+                    "gcoeff_per_s_per_direction": round(2 * coeffs / (ms * 1e-3) / 1e9, 2),
+                    "butterflies_per_s": round(2 * coeffs / 2 * (n.bit_length() - 1) / (ms * 1e-3), 0),
+                    "roofline": {"bound": "hbm", "achieved": round(gbs, 1), "peak": hbm_peak, "unit": "GB/s",
+                                 "frac": round(gbs / hbm_peak, 4), "traffic": None}})
+        # data must survive the round trip bit for bit (size-independent property at full size)
+        back = m.to_rns()
+        assert np.array_equal(back, host), "NTT round trip changed the data"
+        del m, params
+    return out
+
+
+def bench_mul_decompose(device, steps, warmup, hbm_peak):
+    """configs[2] (C3-a): S(1x30) * G^-1(other 1x30), n=2^14, 15x24-bit limbs, base 2^12."""
+    from mxx_b200 import GpuDCRTPolyMatrix, ffi
+
+    cfg = C3A
+    params, moduli = make_params(cfg, device)
+    n, Lm = cfg["n"], cfg["depth"]
+    dpt = -(-cfg["bits"] // cfg["bb"])
+    ell = dpt * Lm
+    m_in = cfg["d"] * ell
+    S = np.empty((cfg["r"], m_in, Lm, n), dtype=np.uint64)
+    O = np.empty((cfg["d"], cfg["c"], Lm, n), dtype=np.uint64)
+    uniform_host(S, moduli, seed=0x6D7878_0003)
+    uniform_host(O, moduli, seed=0x6D7878_0004)
+    gS, gO = GpuDCRTPolyMatrix.from_rns(params, S), GpuDCRTPolyMatrix.from_rns(params, O)
+    out = GpuDCRTPolyMatrix(params, cfg["r"], cfg["c"])
+    L = ffi.lib()
+
+    def step():
+        ffi.check_status(L.gpu_matrix_mul_decompose(out.raw, gS.raw, gO.raw, cfg["bb"], 0), "gpu_matrix_mul_decompose")
+
+    ms = timed(params, LocalDist(), step, steps, warmup) / steps
+    t0 = time.perf_counter()
+    seq = gS.mul_decompose(gO, fused=False)
+    params.synchronize()
+    seq_ms = (time.perf_counter() - t0) * 1e3
+    assert seq == out, "fused mul_decompose differs from the reference call sequence"
+    W = 4
+    logn = n.bit_length() - 1
+    butterflies = (cfg["d"] * cfg["c"] * Lm + m_in * cfg["c"] * Lm) * (n // 2) * logn
+    macs = cfg["r"] * m_in * cfg["c"] * Lm * n
+    min_bytes = W * Lm * n * (cfg["r"] * m_in + cfg["d"] * cfg["c"] + cfg["r"] * cfg["c"])
+    return {"workload": "C3-a mul_decompose S(1x30)*G^-1(1x30) n=2^14 L=15x24-bit bb=12", "ms_fused": round(ms, 4),
+            "mul_decompose_per_s": round(1e3 / ms, 2), "ms_reference_call_sequence": round(seq_ms, 3),
+            "modmul_per_s": round((butterflies + macs) / (ms * 1e-3), 0), "butterflies": butterflies, "macs": macs,
+            "min_hbm_bytes": min_bytes, "hbm_frac_of_min_bytes": round(min_bytes / (ms * 1e-3) / 1e9 / hbm_peak, 4)}
+
+
+def cpu_matmul_baseline(A, B, moduli, n, reps):
+    """the oracle port of the reference CPU loop (src/matrix/base/memory.rs:589-605), all host threads"""
+    from oracle import oracle as orc
+
+    plan = orc.Plan(n, moduli)
+    threads = orc.lib().orc_get_threads()
+    plan.mul(A[:, :2], B[:2, :4])  # warm-up on a corner
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        out = plan.mul(A, B)
+    dt = (time.perf_counter() - t0) / reps
+    return dt, threads, out
+
+
+def run_gpu(args):
+    from mxx_b200 import GPU_POLY_FORMAT_EVAL, GpuDCRTPolyMatrix, PinnedBuffer, ffi
+
+    dist = Dist(args.gpus)
+    device = dist.local_rank
+    hbm_peak, peak_src = peaks()
+    cfg = C1R
+    params, moduli = make_params(cfg, device)
+    n, Lm, r, k, c = cfg["n"], cfg["depth"], cfg["r"], cfg["k"], cfg["c"]
+    L = ffi.lib()
+
+    # synthetic operands, generated straight into pinned host memory (the e2e leg copies from there)
+    pinA, pinB, pinO = PinnedBuffer((r, k, Lm, n)), PinnedBuffer((k, c, Lm, n)), PinnedBuffer((r, c, Lm, n))
+    uniform_host(pinA.array, moduli, seed=0x6D7878_0001 + 2 * dist.rank)
+    uniform_host(pinB.array, moduli, seed=0x6D7878_0001 + 2 * dist.rank + 1)
+    gA, gB = GpuDCRTPolyMatrix(params, r, k), GpuDCRTPolyMatrix(params, k, c)
+    gO = GpuDCRTPolyMatrix(params, r, c)
+    gA.load_rns(pinA.array, GPU_POLY_FORMAT_EVAL)
+    gB.load_rns(pinB.array, GPU_POLY_FORMAT_EVAL)
+
+    def step():
+        ffi.check_status(L.gpu_matrix_mul(gO.raw, gA.raw, gB.raw), "gpu_matrix_mul")
+
+    # ---- device-resident throughput (value) --------------------------------------------------
+    launches0 = L.gpu_kernel_launch_count()
+    with ClockSampler(device) as clk:
+        total_ms = timed(params, dist, step, args.steps, args.warmup)
+    launches = (L.gpu_kernel_launch_count() - launches0) * args.steps // (args.steps + args.warmup)
+    ms_per_step = total_ms / args.steps
+    value = dist.world * 1e3 / ms_per_step
+    W = 4  # u32 residues on the device: every modulus is below 2^30
+    algo_bytes = W * Lm * n * (r * k + k * c + r * c)  # each operand read once, result written once
+    achieved = algo_bytes / (ms_per_step * 1e-3) / 1e9
+
+    # ---- end to end through the C ABI with host buffers ----------------------------------------
+    def e2e_step():
+        gA.load_rns(pinA.array, GPU_POLY_FORMAT_EVAL, wait=True)
+        gB.load_rns(pinB.array, GPU_POLY_FORMAT_EVAL, wait=True)
+        step()
+        gO.store_rns(pinO.array, GPU_POLY_FORMAT_EVAL, wait=True)
+
+    e2e_steps = max(1, min(args.steps, 10))
+    for _ in range(2):
+        e2e_step()
+    params.synchronize()
+    dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    params.synchronize()
+    e2e_s = dist.max(time.perf_counter() - t0)
+    dist.barrier()
+    e2e_value = dist.world * e2e_steps / e2e_s
+    result_host = pinO.array.copy()
+
+    line = {
+        "metric": "DCRT matrix-muls/s", "value": round(value, 2), "unit": "matrix-muls/s", "n_gpus": dist.world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+        "config": {"workload": "C1-R bench_matrix_mul: DCRTPolyMatrix 1x30 * 30x120, n=2^14, 15 CRT limbs x 24 bit, EVAL operands "
+                               "(benches/bench_matrix_mul_cpu.rs:10-16)", "ring_dim": n, "limbs": Lm, "crt_bits": cfg["bits"],
+                   "shape": [r, k, c], "per_gpu": "one independent product per rank", "l2": "inputs (3.57 GB) exceed the 126 MB L2"},
+        "e2e": {"value": round(e2e_value, 3), "unit": "matrix-muls/s", "h2d_bytes_per_step": int(pinA.nbytes + pinB.nbytes),
+                "d2h_bytes_per_step": int(pinO.nbytes), "steps": e2e_steps,
+                "path": "gpu_matrix_load_rns_batch x2 (pinned host u64) -> gpu_matrix_mul -> gpu_matrix_store_rns_batch -> gpu_event_set_wait"},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "kernel": "matmul_kernel<u32,4,1,4>", "achieved": round(achieved, 1), "peak": hbm_peak,
+                     "unit": "GB/s", "frac": round(achieved / hbm_peak, 4), "traffic": None, "algorithmic_bytes": algo_bytes,
+                     "peak_source": peak_src},
+        "clocks": clk.summary(),
+    }
+
+    if dist.rank == 0 and dist.world == 1:
+        # CPU baseline beside it: same operands, all host threads, and a parity check of the GPU result
+        if not args.no_cpu:
+            reps = 3
+            dt, threads, cpu_out = cpu_matmul_baseline(pinA.array, pinB.array, moduli, n, reps)
+            assert np.array_equal(cpu_out, result_host), "GPU result differs from the CPU oracle"
+            line["cpu_baseline"] = {"value": round(1.0 / dt, 4), "unit": "matrix-muls/s", "cores": threads, "kind": "port",
+                                    "sample": f"the full C1-R product x{reps} (oracle/dcrt_oracle.c orc_matrix_mul, OpenMP)",
+                                    "parity": "bit-exact vs GPU result"}
+        del gA, gB, gO
+        pinB.free()
+        if not args.no_extras:
+            line["ntt"] = bench_ntt(device, max(3, min(args.steps, 20)), args.warmup, hbm_peak)
+            line["mul_decompose"] = bench_mul_decompose(device, max(3, min(args.steps, 20)), args.warmup, hbm_peak)
+    if dist.rank == 0:
+        print(json.dumps(line), flush=True)
+    dist.close()
+
+
+def run_reference(args):
+    """reference arm: the reference's CPU algorithm for the same workload on the host cores.
+    OpenFHE / cargo are absent, so this is the oracle port; rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    from mxx_b200.params import standard_moduli
+
+    cfg = C1R
+    n, Lm, r, k, c = cfg["n"], cfg["depth"], cfg["r"], cfg["k"], cfg["c"]
+    moduli = standard_moduli(n, Lm, cfg["bits"])
+    A = np.empty((r, k, Lm, n), dtype=np.uint64)
+    B = np.empty((k, c, Lm, n), dtype=np.uint64)
+    uniform_host(A, moduli, seed=0x6D7878_0001)
+    uniform_host(B, moduli, seed=0x6D7878_0002)
+    from oracle import oracle as orc
+
+    plan = orc.Plan(n, moduli)
+    threads = orc.lib().orc_get_threads()
+    steps, warmup = min(args.steps, 20), min(args.warmup, 3)
+    for _ in range(warmup):
+        plan.mul(A, B)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        plan.mul(A, B)
+    dt = (time.perf_counter() - t0) / steps
+    v = round(1.0 / dt, 4)
+    line = {"impl": "reference", "metric": "DCRT matrix-muls/s", "value": v, "unit": "matrix-muls/s", "n_gpus": args.gpus,
+            "steps": steps, "warmup": warmup, "ms_per_step": round(dt * 1e3, 3), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "config": {"workload": "C1-R bench_matrix_mul: DCRTPolyMatrix 1x30 * 30x120, n=2^14, 15 CRT limbs x 24 bit, EVAL operands "
+                                   "(benches/bench_matrix_mul_cpu.rs:10-16)", "ring_dim": n, "limbs": Lm, "crt_bits": cfg["bits"], "shape": [r, k, c]},
+            "cpu_baseline": {"value": v, "unit": "matrix-muls/s", "cores": threads, "kind": "port",
+                             "sample": f"the full C1-R product, {steps} timed steps (oracle port of src/matrix/base/memory.rs:589-605; "
+                                       "the reference's own OpenFHE path is unavailable on this box)"},
+            "e2e": {"value": v, "unit": "matrix-muls/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg (profiling runs)")
+    ap.add_argument("--no-extras", action="store_true", help="skip the NTT and mul_decompose sections (profiling runs)")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -128,6 +128,14 @@ void *gpu_context_stream(const GpuContext *ctx);
 int gpu_matrix_device_info(const GpuMatrix *mat, void **out_ptr, int *out_word_bytes, int *out_format);
 /* Number of kernels launched by this library since process start (bench.py's gpu_launches). */
 uint64_t gpu_kernel_launch_count(void);
+/* CUDA-event stopwatch on the context stream: record(stop=0), work, record(stop=1), elapsed. */
+typedef struct GpuTimer GpuTimer;
+int gpu_timer_create(const GpuContext *ctx, GpuTimer **out);
+int gpu_timer_record(const GpuContext *ctx, GpuTimer *timer, int stop);
+int gpu_timer_elapsed_ms(GpuTimer *timer, float *out_ms);
+void gpu_timer_destroy(GpuTimer *timer);
+/* Waits for the context stream only (gpu_device_synchronize waits for the whole device). */
+int gpu_context_synchronize(const GpuContext *ctx);
 
 #ifdef __cplusplus
 }

@@ -225,4 +225,51 @@ void gpu_pinned_free(void *ptr) {
 
 uint64_t gpu_kernel_launch_count(void) { return gp::g_launches.load(); }
 
+// ---- extension: CUDA-event stopwatch on the context stream (bench.py times kernels with it) ----
+struct GpuTimer {
+    cudaEvent_t start = nullptr, stop = nullptr;
+    int device = 0;
+};
+int gpu_timer_create(const GpuContext *ctx, GpuTimer **out) {
+    if (!ctx || !out) return gp::set_error("invalid gpu_timer_create arguments");
+    GP_CUDA(cudaSetDevice(ctx->device), "cudaSetDevice");
+    GpuTimer *t = new GpuTimer();
+    t->device = ctx->device;
+    cudaError_t e = cudaEventCreate(&t->start);
+    if (e == cudaSuccess) e = cudaEventCreate(&t->stop);
+    if (e != cudaSuccess) {
+        if (t->start) cudaEventDestroy(t->start);
+        delete t;
+        return gp::set_cuda_error(e, "cudaEventCreate");
+    }
+    *out = t;
+    return 0;
+}
+int gpu_timer_record(const GpuContext *ctx, GpuTimer *t, int stop) {
+    if (!ctx || !t) return gp::set_error("invalid gpu_timer_record arguments");
+    GP_CUDA(cudaSetDevice(ctx->device), "cudaSetDevice");
+    GP_CUDA(cudaEventRecord(stop ? t->stop : t->start, ctx->stream), "cudaEventRecord");
+    return 0;
+}
+int gpu_timer_elapsed_ms(GpuTimer *t, float *out_ms) {
+    if (!t || !out_ms) return gp::set_error("invalid gpu_timer_elapsed_ms arguments");
+    GP_CUDA(cudaSetDevice(t->device), "cudaSetDevice");
+    GP_CUDA(cudaEventSynchronize(t->stop), "cudaEventSynchronize");
+    GP_CUDA(cudaEventElapsedTime(out_ms, t->start, t->stop), "cudaEventElapsedTime");
+    return 0;
+}
+void gpu_timer_destroy(GpuTimer *t) {
+    if (!t) return;
+    cudaSetDevice(t->device);
+    cudaEventDestroy(t->start);
+    cudaEventDestroy(t->stop);
+    delete t;
+}
+int gpu_context_synchronize(const GpuContext *ctx) {
+    if (!ctx) return gp::set_error("invalid gpu_context_synchronize arguments");
+    GP_CUDA(cudaSetDevice(ctx->device), "cudaSetDevice");
+    GP_CUDA(cudaStreamSynchronize(ctx->stream), "cudaStreamSynchronize");
+    return 0;
+}
+
 }  // extern "C"

@@ -78,6 +78,11 @@ EXTENSIONS = {
     "gpu_context_stream": (C.c_void_p, [H]),
     "gpu_matrix_device_info": (C.c_int, [H, vpp, intp, intp]),
     "gpu_kernel_launch_count": (C.c_uint64, []),
+    "gpu_timer_create": (C.c_int, [H, vpp]),
+    "gpu_timer_record": (C.c_int, [H, H, C.c_int]),
+    "gpu_timer_elapsed_ms": (C.c_int, [H, C.POINTER(C.c_float)]),
+    "gpu_timer_destroy": (None, [H]),
+    "gpu_context_synchronize": (C.c_int, [H]),
 }
 
 

@@ -106,6 +106,12 @@ class GpuDCRTPolyParams:
         """cudaStream_t all work of this context is ordered on (extension)."""
         return int(self._L.gpu_context_stream(self._ctx) or 0)
 
+    def synchronize(self) -> None:
+        ffi.check_status(self._L.gpu_context_synchronize(self._ctx), "gpu_context_synchronize", self._L)
+
+    def timer(self) -> "GpuTimer":
+        return GpuTimer(self)
+
     def close(self) -> None:
         if getattr(self, "_ctx", None):
             self._L.gpu_context_destroy(self._ctx)
@@ -114,5 +120,35 @@ class GpuDCRTPolyParams:
     def __del__(self):  # Drop for GpuContext, gpu.rs:695-705
         try:
             self.close()
+        except Exception:
+            pass
+
+
+class GpuTimer:
+    """CUDA-event stopwatch on the context stream (extension gpu_timer_*)."""
+
+    def __init__(self, params: GpuDCRTPolyParams):
+        self._p = params
+        self._L = params._L
+        h = C.c_void_p()
+        ffi.check_status(self._L.gpu_timer_create(params.ctx_raw(), C.byref(h)), "gpu_timer_create", self._L)
+        self._h = h
+
+    def start(self):
+        ffi.check_status(self._L.gpu_timer_record(self._p.ctx_raw(), self._h, 0), "gpu_timer_record", self._L)
+
+    def stop(self):
+        ffi.check_status(self._L.gpu_timer_record(self._p.ctx_raw(), self._h, 1), "gpu_timer_record", self._L)
+
+    def elapsed_ms(self) -> float:
+        ms = C.c_float(0)
+        ffi.check_status(self._L.gpu_timer_elapsed_ms(self._h, C.byref(ms)), "gpu_timer_elapsed_ms", self._L)
+        return float(ms.value)
+
+    def __del__(self):
+        try:
+            if self._h:
+                self._L.gpu_timer_destroy(self._h)
+                self._h = None
         except Exception:
             pass
