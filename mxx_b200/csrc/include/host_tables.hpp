@@ -110,6 +110,7 @@ Tables<T> build_tables(int logN, const std::vector<uint64_t> &moduli, const std:
         const uint64_t r64 = (uint64_t)((((u128)1) << 64) % q);
         c.r64 = (T)r64;
         c.r64_s = shoup<T>(r64, q);
+        c.one_s = (T)((((u128)1) << (sizeof(T) * 8)) / q);
         c.mu64 = (uint64_t)((((u128)1) << 64) / q);
         c.bits = 64 - (uint32_t)__builtin_clzll(q);
         c.pad = 0;
@@ -128,6 +129,8 @@ inline uint32_t mac_fold_terms(uint64_t qmax, bool wide) {
 }
 // storage width rule: u32 words when every modulus is below 2^30 (lazy values stay below 4q < 2^32)
 inline bool needs_wide(uint64_t qmax) { return qmax >= (1ull << 30); }
+// forward transforms need no conditional subtraction when 36*q fits the word (ntt_fast.cuh)
+inline bool nocsub_ok(uint64_t qmax, bool wide) { return wide ? qmax < ((uint64_t)1 << 58) : qmax * 36 < ((uint64_t)1 << 32); }
 
 }  // namespace host
 }  // namespace gp

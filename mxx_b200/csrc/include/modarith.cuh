@@ -41,6 +41,7 @@ template <typename T> struct LimbConst {
     T ninv, ninv_s;  // n^-1 mod q and its Shoup companion
     T nw, nw_s;      // n^-1 * psi^-bitrev(1): merged last inverse-stage twiddle
     T r64, r64_s;    // 2^64 mod q (+ Shoup), folds the high word of a 128-bit sum
+    T one_s;         // floor(2^wordbits / q): Shoup companion of 1 (any word -> [0,2q))
     uint64_t mu64;   // floor(2^64 / q): Barrett constant for 64-bit inputs
     uint32_t bits;   // bit width of q
     uint32_t pad;

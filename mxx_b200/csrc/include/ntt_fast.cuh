@@ -1,0 +1,407 @@
+// ntt_fast.cuh — compile-time-planned negacyclic NTT / INTT for the ring sizes that matter
+// (one (poly, limb) block of 2^LOGB words resident in shared memory, LOGB = 12..15).
+//
+// Same mathematics and tables as ntt.cuh (merged-psi Cooley-Tukey forward, Gentleman-Sande
+// inverse, Shoup twiddles, device EVAL order bit-reversed); what changes is the schedule:
+//
+//   forward  pass 1   global -> radix-2^R1 in registers -> smem      (coalesced 4/8-byte loads)
+//            pass 2.. smem -> radix-16 -> smem                       (K passes)
+//            last     smem (128-bit) -> radix-4 on 4 consecutive words -> global (128-bit)
+//   inverse  the mirror image: 128-bit global loads -> radix-4 -> smem ... -> radix-2^R1 -> global
+//
+//   * every stride is a template constant, so shared-memory addresses are base + immediate:
+//     no per-access index arithmetic (the v1 kernel spent more issue slots on LEA/SHF than on
+//     butterflies, profiles/r01_ncu_v1_summary.md);
+//   * padding of one 16-byte vector per 64 words keeps all passes bank-conflict free AND keeps
+//     128-bit alignment for the vector pass; u64 residues live as two u32 planes (lo / hi) so
+//     the u64 path has exactly the u32 access pattern;
+//   * 256 threads and <= 80 registers: three CTAs per SM for a 64 KB block, so one CTA's
+//     global loads overlap the other two CTAs' butterflies;
+//   * NOCSUB: when 34*q < 2^wordbits (24..26-bit and 51-bit moduli) the forward transform needs
+//     no conditional subtraction at all (values grow by 2q per stage and the Shoup multiply
+//     accepts any word); one Shoup-by-one reduction at the final store brings them to [0, q).
+#pragma once
+#include "modarith.cuh"
+#include "ntt.cuh"
+
+namespace gp {
+
+// ---- shared-memory view ---------------------------------------------------------------
+GP_HD uint32_t padw(uint32_t a) { return a + ((a >> 6) << 2); }
+template <int LOGB> struct FastGeom {
+    static constexpr uint32_t B = 1u << LOGB;
+    static constexpr uint32_t kPlane = B + ((B >> 6) << 2);  // padded words per plane
+    // stage split: LOGB = R1 + 4*K + 2
+    static constexpr int kRem = LOGB - 2;
+    static constexpr int kR1 = (kRem % 4 == 0) ? 4 : ((kRem % 4 == 1 && kRem >= 5) ? 5 : kRem % 4);
+    static constexpr int kK = (kRem - kR1) / 4;
+    static_assert(kR1 >= 1 && kR1 <= 5 && kK >= 0 && LOGB - kR1 >= 6, "unsupported block size");
+};
+template <typename T, int LOGB> constexpr size_t fast_smem_bytes() {
+    return (size_t)FastGeom<LOGB>::kPlane * sizeof(uint32_t) * (sizeof(T) / 4);
+}
+
+template <typename T, int LOGB> struct SmemView;
+template <int LOGB> struct SmemView<uint32_t, LOGB> {
+    uint32_t *p;
+    GP_HD explicit SmemView(void *base) : p(reinterpret_cast<uint32_t *>(base)) {}
+    GP_HD uint32_t ld(uint32_t i) const { return p[i]; }
+    GP_HD void st(uint32_t i, uint32_t v) const { p[i] = v; }
+    GP_HD void ld4(uint32_t i, uint32_t (&x)[4]) const {
+        const uint4 v = *reinterpret_cast<const uint4 *>(p + i);
+        x[0] = v.x, x[1] = v.y, x[2] = v.z, x[3] = v.w;
+    }
+    GP_HD void st4(uint32_t i, const uint32_t (&x)[4]) const { *reinterpret_cast<uint4 *>(p + i) = make_uint4(x[0], x[1], x[2], x[3]); }
+};
+template <int LOGB> struct SmemView<uint64_t, LOGB> {
+    uint32_t *lo, *hi;
+    GP_HD explicit SmemView(void *base)
+        : lo(reinterpret_cast<uint32_t *>(base)), hi(reinterpret_cast<uint32_t *>(base) + FastGeom<LOGB>::kPlane) {}
+    GP_HD uint64_t ld(uint32_t i) const { return ((uint64_t)hi[i] << 32) | lo[i]; }
+    GP_HD void st(uint32_t i, uint64_t v) const { lo[i] = (uint32_t)v, hi[i] = (uint32_t)(v >> 32); }
+    GP_HD void ld4(uint32_t i, uint64_t (&x)[4]) const {
+        const uint4 a = *reinterpret_cast<const uint4 *>(lo + i), b = *reinterpret_cast<const uint4 *>(hi + i);
+        x[0] = ((uint64_t)b.x << 32) | a.x, x[1] = ((uint64_t)b.y << 32) | a.y;
+        x[2] = ((uint64_t)b.z << 32) | a.z, x[3] = ((uint64_t)b.w << 32) | a.w;
+    }
+    GP_HD void st4(uint32_t i, const uint64_t (&x)[4]) const {
+        *reinterpret_cast<uint4 *>(lo + i) = make_uint4((uint32_t)x[0], (uint32_t)x[1], (uint32_t)x[2], (uint32_t)x[3]);
+        *reinterpret_cast<uint4 *>(hi + i) = make_uint4((uint32_t)(x[0] >> 32), (uint32_t)(x[1] >> 32), (uint32_t)(x[2] >> 32), (uint32_t)(x[3] >> 32));
+    }
+};
+
+// 4 consecutive words from / to global memory (16 bytes for u32, 32 bytes for u64)
+GP_HD void gld4(const uint32_t *p, uint32_t (&x)[4]) {
+    const uint4 v = *reinterpret_cast<const uint4 *>(p);
+    x[0] = v.x, x[1] = v.y, x[2] = v.z, x[3] = v.w;
+}
+GP_HD void gld4(const uint64_t *p, uint64_t (&x)[4]) {
+    const ulonglong2 a = *reinterpret_cast<const ulonglong2 *>(p), b = *reinterpret_cast<const ulonglong2 *>(p + 2);
+    x[0] = a.x, x[1] = a.y, x[2] = b.x, x[3] = b.y;
+}
+GP_HD void gst4(uint32_t *p, const uint32_t (&x)[4]) { *reinterpret_cast<uint4 *>(p) = make_uint4(x[0], x[1], x[2], x[3]); }
+GP_HD void gst4(uint64_t *p, const uint64_t (&x)[4]) {
+    *reinterpret_cast<ulonglong2 *>(p) = make_ulonglong2(x[0], x[1]);
+    *reinterpret_cast<ulonglong2 *>(p + 2) = make_ulonglong2(x[2], x[3]);
+}
+
+// unsigned min trick: x - m wraps to a huge value when x < m
+template <typename T> GP_HD T csub_min(T x, T m) {
+    const T y = x - m;
+    return y < x ? y : x;
+}
+// any word -> [0, 2q): Shoup multiplication by one, one_s = floor(2^wordbits / q)
+template <typename T> GP_HD T reduce_lazy(T x, T one_s, T q) { return x - mulhi(x, one_s) * q; }
+
+// ---- butterfly networks ---------------------------------------------------------------------
+// Forward (Cooley-Tukey): stage s pairs j and j + (R >> (s+1)); twiddle index (twbase << s) + u.
+// NOCSUB: inputs < B give outputs < B + 2q*LOGR; otherwise values stay in [0, 4q).
+template <typename T, int LOGR, bool NOCSUB>
+GP_HD void fwd_net(T (&x)[1 << LOGR], const TwPair<T> *__restrict__ tw, uint32_t twbase, T q, T q2) {
+    constexpr int R = 1 << LOGR;
+#pragma unroll
+    for (int s = 0; s < LOGR; s++) {
+        const int half = R >> (s + 1);
+#pragma unroll
+        for (int u = 0; u < (1 << s); u++) {
+            const TwPair<T> w = tw[(twbase << s) + u];
+#pragma unroll
+            for (int v = 0; v < half; v++) {
+                const int j0 = u * 2 * half + v, j1 = j0 + half;
+                const T X = NOCSUB ? x[j0] : csub_min<T>(x[j0], q2);
+                const T t = mul_shoup_lazy<T>(x[j1], w.w, w.ws, q);
+                x[j0] = X + t;
+                x[j1] = X - t + q2;
+            }
+        }
+    }
+}
+// Inverse (Gentleman-Sande): stage s pairs j and j + (1 << s); inputs and outputs in [0, 2q).
+// FINAL merges n^-1 (and n^-1 * last twiddle) into the last stage.
+template <typename T, int LOGR, bool FINAL>
+GP_HD void inv_net(T (&x)[1 << LOGR], const TwPair<T> *__restrict__ tw, uint32_t twbase, const LimbConst<T> &c) {
+    constexpr int R = 1 << LOGR;
+    const T q = c.q, q2 = c.q2;
+#pragma unroll
+    for (int s = 0; s < LOGR; s++) {
+        const int groups = R >> (s + 1);
+#pragma unroll
+        for (int u = 0; u < groups; u++) {
+            if (FINAL && s == LOGR - 1) {
+#pragma unroll
+                for (int v = 0; v < (1 << s); v++) {
+                    const int j0 = u * (2 << s) + v, j1 = j0 + (1 << s);
+                    const T X = x[j0], Y = x[j1];
+                    x[j0] = mul_shoup_lazy<T>(X + Y, c.ninv, c.ninv_s, q);
+                    x[j1] = mul_shoup_lazy<T>(X - Y + q2, c.nw, c.nw_s, q);
+                }
+            } else {
+                const TwPair<T> w = tw[twbase * groups + u];
+#pragma unroll
+                for (int v = 0; v < (1 << s); v++) {
+                    const int j0 = u * (2 << s) + v, j1 = j0 + (1 << s);
+                    const T X = x[j0], Y = x[j1];
+                    x[j0] = csub_min<T>(X + Y, q2);
+                    x[j1] = mul_shoup_lazy<T>(X - Y + q2, w.w, w.ws, q);
+                }
+            }
+        }
+    }
+}
+
+// ---- passes over one block of B = 2^LOGB words -------------------------------------------------
+// Conventions: `nblk` = number of B-blocks in the whole transform (n / B), `sb` = this block's
+// index; forward twiddle index of a span-block = (#span-blocks in the transform) + (its index).
+
+// padded offset of j*stride for a stride that is a multiple of 64 words or smaller than 64
+template <int LSTRIDE> GP_HD constexpr uint32_t joff(int j) {
+    return LSTRIDE >= 6 ? padw((uint32_t)j << LSTRIDE) : ((uint32_t)j << LSTRIDE);
+}
+
+// forward pass 1: source functor -> radix-2^R1 -> smem
+template <typename T, int LOGB, bool NOCSUB, class Src>
+GP_HD void f_first(const Src &src, const SmemView<T, LOGB> &sm, const TwPair<T> *__restrict__ tw, uint32_t nblk, uint32_t sb,
+                   T q, T q2) {
+    constexpr int R1 = FastGeom<LOGB>::kR1, R = 1 << R1, LST = LOGB - R1;
+    constexpr uint32_t stride = 1u << LST;
+#pragma unroll 2
+    for (uint32_t g = GP_TID; g < stride; g += GP_NT) {
+        T x[R];
+#pragma unroll
+        for (int j = 0; j < R; j++) x[j] = src(g + j * stride);
+        fwd_net<T, R1, NOCSUB>(x, tw, nblk + sb, q, q2);
+        const uint32_t base = padw(g);
+#pragma unroll
+        for (int j = 0; j < R; j++) sm.st(base + joff<LST>(j), x[j]);
+    }
+}
+// forward smem pass: radix 16 at stride 2^(LSPAN-4)
+template <typename T, int LOGB, int LSPAN, bool NOCSUB>
+GP_HD void f_mid(const SmemView<T, LOGB> &sm, const TwPair<T> *__restrict__ tw, uint32_t nblk, uint32_t sb, T q, T q2) {
+    constexpr int LST = LSPAN - 4;
+    constexpr uint32_t stride = 1u << LST, groups = 1u << (LOGB - 4);
+    constexpr uint32_t per = LOGB - LSPAN;  // log2(span-blocks per B-block)
+#pragma unroll 2
+    for (uint32_t g = GP_TID; g < groups; g += GP_NT) {
+        const uint32_t b = g >> LST, e = g & (stride - 1);
+        const uint32_t base = padw((b << LSPAN) + e);
+        T x[16];
+#pragma unroll
+        for (int j = 0; j < 16; j++) x[j] = sm.ld(base + joff<LST>(j));
+        fwd_net<T, 4, NOCSUB>(x, tw, ((nblk + sb) << per) + b, q, q2);
+#pragma unroll
+        for (int j = 0; j < 16; j++) sm.st(base + joff<LST>(j), x[j]);
+    }
+}
+// forward last pass: 4 consecutive words (one 128-bit smem vector) -> radix 4 -> [0,q) -> global
+template <typename T, int LOGB, bool NOCSUB, int STAGES>
+GP_HD void f_last(const SmemView<T, LOGB> &sm, T *__restrict__ dst, const TwPair<T> *__restrict__ tw, uint32_t nblk, uint32_t sb,
+                  const LimbConst<T> &c) {
+    constexpr uint32_t groups = 1u << (LOGB - 2);
+    const T q = c.q, q2 = c.q2;
+#pragma unroll 2
+    for (uint32_t g = GP_TID; g < groups; g += GP_NT) {
+        T x[4];
+        sm.ld4(4 * g + ((g >> 4) << 2), x);
+        fwd_net<T, 2, NOCSUB>(x, tw, ((nblk + sb) << (LOGB - 2)) + g, q, q2);
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            T v = x[j];
+            if (NOCSUB) {
+                // < (1 + 2*STAGES) q: one Shoup-by-one brings it to [0, 2q)
+                v = reduce_lazy<T>(v, c.one_s, q);
+            } else {
+                v = csub_min<T>(v, q2);
+            }
+            x[j] = csub_min<T>(v, q);
+        }
+        gst4(dst + 4 * g, x);
+    }
+}
+
+// inverse first pass: global (128-bit) -> radix 4 on 4 consecutive words -> smem
+template <typename T, int LOGB>
+GP_HD void i_first(const T *__restrict__ src, const SmemView<T, LOGB> &sm, const TwPair<T> *__restrict__ tw, uint32_t nblk,
+                   uint32_t sb, const LimbConst<T> &c) {
+    constexpr uint32_t groups = 1u << (LOGB - 2);
+#pragma unroll 2
+    for (uint32_t g = GP_TID; g < groups; g += GP_NT) {
+        T x[4];
+        gld4(src + 4 * g, x);
+        inv_net<T, 2, false>(x, tw, ((nblk + sb) << (LOGB - 2)) + g, c);
+        sm.st4(4 * g + ((g >> 4) << 2), x);
+    }
+}
+// inverse smem pass: radix 16 at distance t0 = 2^LT0 (block span 2^(LT0+4))
+template <typename T, int LOGB, int LT0>
+GP_HD void i_mid(const SmemView<T, LOGB> &sm, const TwPair<T> *__restrict__ tw, uint32_t nblk, uint32_t sb, const LimbConst<T> &c) {
+    constexpr int LSPAN = LT0 + 4;
+    constexpr uint32_t t0 = 1u << LT0, groups = 1u << (LOGB - 4);
+    constexpr uint32_t per = LOGB - LSPAN;
+#pragma unroll 2
+    for (uint32_t g = GP_TID; g < groups; g += GP_NT) {
+        const uint32_t b = g >> LT0, e = g & (t0 - 1);
+        const uint32_t base = padw((b << LSPAN) + e);
+        T x[16];
+#pragma unroll
+        for (int j = 0; j < 16; j++) x[j] = sm.ld(base + joff<LT0>(j));
+        inv_net<T, 4, false>(x, tw, ((nblk + sb) << per) + b, c);
+#pragma unroll
+        for (int j = 0; j < 16; j++) sm.st(base + joff<LT0>(j), x[j]);
+    }
+}
+// inverse last pass: smem -> radix-2^R1 over the whole block -> global; FINAL merges n^-1
+template <typename T, int LOGB, bool FINAL>
+GP_HD void i_last(const SmemView<T, LOGB> &sm, T *__restrict__ dst, const TwPair<T> *__restrict__ tw, uint32_t nblk, uint32_t sb,
+                  const LimbConst<T> &c) {
+    constexpr int R1 = FastGeom<LOGB>::kR1, R = 1 << R1, LT0 = LOGB - R1;
+    constexpr uint32_t t0 = 1u << LT0;
+#pragma unroll 2
+    for (uint32_t g = GP_TID; g < t0; g += GP_NT) {
+        const uint32_t base = padw(g);
+        T x[R];
+#pragma unroll
+        for (int j = 0; j < R; j++) x[j] = sm.ld(base + joff<LT0>(j));
+        inv_net<T, R1, FINAL>(x, tw, nblk + sb, c);
+#pragma unroll
+        for (int j = 0; j < R; j++) dst[g + j * t0] = csub_min<T>(x[j], c.q);
+    }
+}
+
+// ---- whole-block transforms ------------------------------------------------------------------------
+template <typename T, int LOGB, bool NOCSUB, class Src>
+GP_HD void fast_fwd_block(const Src &src, T *__restrict__ dst, void *smem, uint32_t logn, uint32_t sb,
+                          const TwPair<T> *__restrict__ tw, const LimbConst<T> &c) {
+    using G = FastGeom<LOGB>;
+    const SmemView<T, LOGB> sm(smem);
+    const uint32_t nblk = 1u << (logn - LOGB);
+    f_first<T, LOGB, NOCSUB>(src, sm, tw, nblk, sb, c.q, c.q2);
+    GP_SYNC();
+    constexpr int S1 = LOGB - G::kR1;  // span after pass 1
+    if constexpr (G::kK >= 1) {
+        f_mid<T, LOGB, S1, NOCSUB>(sm, tw, nblk, sb, c.q, c.q2);
+        GP_SYNC();
+    }
+    if constexpr (G::kK >= 2) {
+        f_mid<T, LOGB, S1 - 4, NOCSUB>(sm, tw, nblk, sb, c.q, c.q2);
+        GP_SYNC();
+    }
+    if constexpr (G::kK >= 3) {
+        f_mid<T, LOGB, S1 - 8, NOCSUB>(sm, tw, nblk, sb, c.q, c.q2);
+        GP_SYNC();
+    }
+    static_assert(G::kK <= 3, "add another f_mid");
+    f_last<T, LOGB, NOCSUB, LOGB>(sm, dst, tw, nblk, sb, c);
+}
+
+template <typename T, int LOGB, bool FINAL>
+GP_HD void fast_inv_block(const T *__restrict__ src, T *__restrict__ dst, void *smem, uint32_t logn, uint32_t sb,
+                          const TwPair<T> *__restrict__ tw, const LimbConst<T> &c) {
+    using G = FastGeom<LOGB>;
+    const SmemView<T, LOGB> sm(smem);
+    const uint32_t nblk = 1u << (logn - LOGB);
+    i_first<T, LOGB>(src, sm, tw, nblk, sb, c);
+    GP_SYNC();
+    if constexpr (G::kK >= 1) {
+        i_mid<T, LOGB, 2>(sm, tw, nblk, sb, c);
+        GP_SYNC();
+    }
+    if constexpr (G::kK >= 2) {
+        i_mid<T, LOGB, 6>(sm, tw, nblk, sb, c);
+        GP_SYNC();
+    }
+    if constexpr (G::kK >= 3) {
+        i_mid<T, LOGB, 10>(sm, tw, nblk, sb, c);
+        GP_SYNC();
+    }
+    i_last<T, LOGB, FINAL>(sm, dst, tw, nblk, sb, c);
+}
+
+// ---- kernels ------------------------------------------------------------------------------------------
+template <typename T, int LOGB> struct FastCfg {
+    static constexpr bool kSmall = fast_smem_bytes<T, LOGB>() <= 72 * 1024;  // three blocks per SM
+    static constexpr int kThreads = kSmall ? 256 : 512;
+    static constexpr int kMinBlocks = kSmall ? (sizeof(T) == 4 ? 3 : 2) : 1;
+};
+// block sizes with a compile-time plan
+template <typename T> inline bool fast_supported(int logb) {
+    return sizeof(T) == 4 ? (logb >= 12 && logb <= 15) : (logb >= 12 && logb <= 14);
+}
+// block size used for a transform of 2^logn words: the whole transform when it fits shared memory,
+// otherwise 64 KB blocks (three CTAs per SM) under radix-2^k global passes
+template <typename T> inline int fast_block_log(int logn) {
+    const int cap = sizeof(T) == 4 ? 15 : 14;
+    return logn <= cap ? logn : cap - 1;
+}
+template <typename T, int LOGB, bool NOCSUB>
+GP_HD void fast_fwd_cta(uint32_t bid, void *smem, const T *src, T *dst, uint32_t limbs, uint32_t logn,
+                        const TwPair<T> *__restrict__ tw_all, const LimbConst<T> *__restrict__ lc) {
+    const uint32_t lsub = logn - LOGB;
+    const size_t pl = bid >> lsub;
+    const uint32_t sb = bid & ((1u << lsub) - 1), limb = (uint32_t)(pl % limbs);
+    const size_t off = (pl << logn) + ((size_t)sb << LOGB);
+    const LimbConst<T> c = lc[limb];
+    PlainSrc<T> s{src + off};
+    fast_fwd_block<T, LOGB, NOCSUB>(s, dst + off, smem, logn, sb, tw_all + ((size_t)limb << logn), c);
+}
+template <typename T, int LOGB, bool NOCSUB>
+__global__ void __launch_bounds__(FastCfg<T, LOGB>::kThreads, FastCfg<T, LOGB>::kMinBlocks)
+fast_ntt_fwd_kernel(const T *src, T *dst, uint32_t limbs, uint32_t logn, const TwPair<T> *__restrict__ tw_all,
+                    const LimbConst<T> *__restrict__ lc) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    fast_fwd_cta<T, LOGB, NOCSUB>(blockIdx.x, smem_raw, src, dst, limbs, logn, tw_all, lc);
+}
+
+template <typename T, int LOGB>
+GP_HD void fast_inv_cta(uint32_t bid, void *smem, const T *src, T *dst, uint32_t limbs, uint32_t logn,
+                        const TwPair<T> *__restrict__ tw_all, const LimbConst<T> *__restrict__ lc) {
+    const uint32_t lsub = logn - LOGB;
+    const size_t pl = bid >> lsub;
+    const uint32_t sb = bid & ((1u << lsub) - 1), limb = (uint32_t)(pl % limbs);
+    const size_t off = (pl << logn) + ((size_t)sb << LOGB);
+    const LimbConst<T> c = lc[limb];
+    const TwPair<T> *tw = tw_all + ((size_t)limb << logn);
+    if (lsub == 0)
+        fast_inv_block<T, LOGB, true>(src + off, dst + off, smem, logn, sb, tw, c);
+    else
+        fast_inv_block<T, LOGB, false>(src + off, dst + off, smem, logn, sb, tw, c);
+}
+template <typename T, int LOGB>
+__global__ void __launch_bounds__(FastCfg<T, LOGB>::kThreads, FastCfg<T, LOGB>::kMinBlocks)
+fast_ntt_inv_kernel(const T *src, T *dst, uint32_t limbs, uint32_t logn, const TwPair<T> *__restrict__ tw_all,
+                    const LimbConst<T> *__restrict__ lc) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    fast_inv_cta<T, LOGB>(blockIdx.x, smem_raw, src, dst, limbs, logn, tw_all, lc);
+}
+
+// fused gadget decomposition + forward NTT (digit extraction is the load functor of pass 1);
+// geometry as decompose_cta in ntt.cuh, block = the whole transform (logn == LOGB)
+template <typename T, int LOGB, bool NOCSUB>
+GP_HD void fast_decompose_cta(uint32_t bid, void *smem, const T *__restrict__ src, T *__restrict__ out, const DecompGeom &g,
+                              const TwPair<T> *__restrict__ tw_all, const LimbConst<T> *__restrict__ lc) {
+    const size_t pl = bid;  // out (poly, limb)
+    const uint32_t limb = (uint32_t)(pl % g.limbs);
+    const size_t opoly = pl / g.limbs;
+    const size_t orow = opoly / g.cols, col = opoly % g.cols;
+    const size_t row = orow / g.ell;
+    const uint32_t loc = (uint32_t)(orow % g.ell), t = loc / g.dpt, dg = loc % g.dpt;
+    const LimbConst<T> c = lc[limb];
+    const uint32_t sbits = lc[t].bits, shift = dg * g.base_bits;
+    T mask = 0;
+    if (shift < sbits) {
+        const uint32_t rem = sbits - shift, db = g.base_bits < rem ? g.base_bits : rem;
+        mask = db >= sizeof(T) * 8 ? ~(T)0 : (T)(((T)1 << db) - 1);
+    }
+    const T *sp = src + (((row * g.src_cols + g.src_col0 + col) * g.limbs + t) << LOGB);
+    DigitSrc<T> dsrc{sp, shift >= sizeof(T) * 8 ? 0u : shift, shift >= sizeof(T) * 8 ? (T)0 : mask, c.q};
+    fast_fwd_block<T, LOGB, NOCSUB>(dsrc, out + (pl << LOGB), smem, LOGB, 0, tw_all + ((size_t)limb << LOGB), c);
+}
+template <typename T, int LOGB, bool NOCSUB>
+__global__ void __launch_bounds__(FastCfg<T, LOGB>::kThreads, FastCfg<T, LOGB>::kMinBlocks)
+fast_decompose_kernel(const T *__restrict__ src, T *__restrict__ out, DecompGeom g, const TwPair<T> *__restrict__ tw_all,
+                      const LimbConst<T> *__restrict__ lc) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    fast_decompose_cta<T, LOGB, NOCSUB>(blockIdx.x, smem_raw, src, out, g, tw_all, lc);
+}
+
+}  // namespace gp

@@ -119,6 +119,8 @@ int gpu_context_create(uint32_t logN, uint32_t L, uint32_t dnum, const uint64_t 
         ctx->crt_bits = 64 - (uint32_t)__builtin_clzll(qmax);
         ctx->wide = needs_wide(qmax);
         ctx->mac_fold = mac_fold_terms(qmax, ctx->wide);
+        ctx->nocsub = nocsub_ok(qmax, ctx->wide);
+        if (const char *env = getenv("MXX_NTT_GENERIC")) ctx->force_generic_ntt = env[0] == '1';
         GP_CUDA(cudaSetDevice(ctx->device), "cudaSetDevice");
         cudaDeviceProp prop;
         GP_CUDA(cudaGetDeviceProperties(&prop, ctx->device), "cudaGetDeviceProperties");

@@ -19,6 +19,7 @@
 #include "arith.cuh"
 #include "host_tables.hpp"
 #include "ntt.cuh"
+#include "ntt_fast.cuh"
 
 namespace {
 using namespace gp;
@@ -31,8 +32,45 @@ template <typename T> struct Emu {
         std::vector<uint64_t> m(moduli, moduli + limbs_), psi;
         for (uint64_t q : m) psi.push_back(host::primitive_2n_root(q, (uint64_t)1 << logn_));
         tab = host::build_tables<T>(logn_, m, psi);
+        uint64_t qmax = 0;
+        for (uint64_t q : m) qmax = q > qmax ? q : qmax;
+        nocsub = host::nocsub_ok(qmax, sizeof(T) == 8);
     }
+    // ---- compile-time-planned kernels (ntt_fast.cuh), same selection rule as MatrixNTT.inl ----
+    bool fast_ok(int logb_cap) const { return logb_cap == 0 && fast_supported<T>(fast_block_log<T>(logn)); }
+    template <int LOGB> void fast_fwd_blocks(std::vector<T> &d, size_t nbid, bool nocsub) {
+        std::vector<uint32_t> sm(fast_smem_bytes<T, LOGB>() / 4 + 4);
+        for (size_t bid = 0; bid < nbid; bid++) {
+            if (nocsub) fast_fwd_cta<T, LOGB, true>((uint32_t)bid, sm.data(), d.data(), d.data(), limbs, logn, tab.fwd.data(), tab.limb.data());
+            else fast_fwd_cta<T, LOGB, false>((uint32_t)bid, sm.data(), d.data(), d.data(), limbs, logn, tab.fwd.data(), tab.limb.data());
+        }
+    }
+    template <int LOGB> void fast_inv_blocks(std::vector<T> &d, size_t nbid) {
+        std::vector<uint32_t> sm(fast_smem_bytes<T, LOGB>() / 4 + 4);
+        for (size_t bid = 0; bid < nbid; bid++)
+            fast_inv_cta<T, LOGB>((uint32_t)bid, sm.data(), d.data(), d.data(), limbs, logn, tab.inv.data(), tab.limb.data());
+    }
+    void fast_fwd_dispatch(std::vector<T> &d, size_t nbid, int logb, bool nocsub) {
+        switch (logb) {
+            case 12: fast_fwd_blocks<12>(d, nbid, nocsub); break;
+            case 13: fast_fwd_blocks<13>(d, nbid, nocsub); break;
+            case 14: fast_fwd_blocks<14>(d, nbid, nocsub); break;
+            default:
+                if constexpr (sizeof(T) == 4) fast_fwd_blocks<15>(d, nbid, nocsub);
+        }
+    }
+    void fast_inv_dispatch(std::vector<T> &d, size_t nbid, int logb) {
+        switch (logb) {
+            case 12: fast_inv_blocks<12>(d, nbid); break;
+            case 13: fast_inv_blocks<13>(d, nbid); break;
+            case 14: fast_inv_blocks<14>(d, nbid); break;
+            default:
+                if constexpr (sizeof(T) == 4) fast_inv_blocks<15>(d, nbid);
+        }
+    }
+    bool nocsub = false;
     int block_log(int logb_cap) const {
+        if (fast_ok(logb_cap)) return fast_block_log<T>(logn);
         int lb = ntt_block_log<T>(logn);
         if (logb_cap > 0 && logb_cap < lb) lb = logb_cap;
         return lb;
@@ -56,6 +94,10 @@ template <typename T> struct Emu {
                 lspan -= passes[i];
             }
         }
+        if (fast_ok(logb_cap)) {
+            fast_fwd_dispatch(d, pl << top, logb, nocsub);
+            return;
+        }
         for (size_t bid = 0; bid < (pl << top); bid++)
             ntt_fwd_cta<T>((uint32_t)bid, sm.data(), d.data(), d.data(), limbs, logn, logb, tab.fwd.data(), tab.limb.data());
     }
@@ -63,8 +105,12 @@ template <typename T> struct Emu {
         const int logb = block_log(logb_cap), top = logn - logb;
         const size_t pl = polys * limbs;
         std::vector<T> sm(ntt_smem_bytes<T>(logb) / sizeof(T) + 1);
-        for (size_t bid = 0; bid < (pl << top); bid++)
-            ntt_inv_cta<T>((uint32_t)bid, sm.data(), d.data(), d.data(), limbs, logn, logb, tab.inv.data(), tab.limb.data());
+        if (fast_ok(logb_cap)) {
+            fast_inv_dispatch(d, pl << top, logb);
+        } else {
+            for (size_t bid = 0; bid < (pl << top); bid++)
+                ntt_inv_cta<T>((uint32_t)bid, sm.data(), d.data(), d.data(), limbs, logn, logb, tab.inv.data(), tab.limb.data());
+        }
         if (top > 0) {
             int passes[8], np = 0;
             split_top(top, passes, &np);
@@ -133,7 +179,29 @@ int do_decompose(int logn, uint32_t limbs, const uint64_t *moduli, const uint64_
     std::vector<T> o(opl << logn);
     const int logb = e.block_log(logb_cap), top = logn - logb;
     std::vector<T> sm(ntt_smem_bytes<T>(logb) / sizeof(T) + 1);
-    if (to_eval && top == 0) {
+    if (to_eval && top == 0 && e.fast_ok(logb_cap)) {
+        std::vector<uint32_t> fsm((sizeof(T) / 4) * ((1u << logb) + (1u << (logb - 4))) + 8);
+#define DEC_CASE(LB)                                                                                                          \
+    case LB:                                                                                                                  \
+        for (size_t bid = 0; bid < opl; bid++) {                                                                              \
+            if (e.nocsub) fast_decompose_cta<T, LB, true>((uint32_t)bid, fsm.data(), s.data(), o.data(), g, e.tab.fwd.data(), e.tab.limb.data()); \
+            else fast_decompose_cta<T, LB, false>((uint32_t)bid, fsm.data(), s.data(), o.data(), g, e.tab.fwd.data(), e.tab.limb.data());         \
+        }                                                                                                                     \
+        break;
+        switch (logb) {
+            DEC_CASE(12)
+            DEC_CASE(13)
+            DEC_CASE(14)
+            default:
+                if constexpr (sizeof(T) == 4) {
+                    for (size_t bid = 0; bid < opl; bid++) {
+                        if (e.nocsub) fast_decompose_cta<T, 15, true>((uint32_t)bid, fsm.data(), s.data(), o.data(), g, e.tab.fwd.data(), e.tab.limb.data());
+                        else fast_decompose_cta<T, 15, false>((uint32_t)bid, fsm.data(), s.data(), o.data(), g, e.tab.fwd.data(), e.tab.limb.data());
+                    }
+                }
+        }
+#undef DEC_CASE
+    } else if (to_eval && top == 0) {
         for (size_t bid = 0; bid < opl; bid++)
             decompose_cta<T, true>((uint32_t)bid, sm.data(), s.data(), o.data(), g, logn, logb, e.tab.fwd.data(), e.tab.limb.data());
     } else {

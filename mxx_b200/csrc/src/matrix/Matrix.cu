@@ -4,6 +4,7 @@
 // Matrix.cu:11-19 includes its MatrixData/Arith/NTT/Decompose/Serde sources; the kernels
 // live in csrc/include/{ntt,arith,serde}.cuh.
 #include <algorithm>
+#include <atomic>
 #include <cstring>
 #include <exception>
 #include <mutex>
@@ -12,6 +13,7 @@
 #include "gpupoly_internal.cuh"
 #include "arith.cuh"
 #include "ntt.cuh"
+#include "ntt_fast.cuh"
 #include "serde.cuh"
 
 #include "MatrixCommon.inl"

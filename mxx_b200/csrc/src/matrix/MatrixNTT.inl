@@ -6,8 +6,74 @@
 
 namespace {
 
-template <typename T> inline int ntt_block_log(const GpuContext *ctx) { return gp::ntt_block_log<T>(ctx->logN); }
+// block (per-CTA) size: the compile-time-planned kernels of ntt_fast.cuh when one exists for this
+// ring, else the generic kernel of ntt.cuh
+template <typename T> inline int ntt_block_log(const GpuContext *ctx) {
+    const int fb = gp::fast_block_log<T>(ctx->logN);
+    if (!ctx->force_generic_ntt && gp::fast_supported<T>(fb)) return fb;
+    return gp::ntt_block_log<T>(ctx->logN);
+}
+template <typename T> inline bool use_fast(const GpuContext *ctx, int logb) {
+    return !ctx->force_generic_ntt && gp::fast_supported<T>(logb) && logb == gp::fast_block_log<T>(ctx->logN);
+}
 using gp::split_top;
+
+// opt-in to > 48 KB of dynamic shared memory, once per kernel instantiation and device
+template <typename K> int optin_smem(K kernel, size_t bytes, int device, std::atomic<uint32_t> &done) {
+    if (bytes <= 48 * 1024) return 0;
+    const uint32_t bit = 1u << (device & 31);
+    if (done.load(std::memory_order_acquire) & bit) return 0;
+    GP_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes), "cudaFuncSetAttribute");
+    done.fetch_or(bit, std::memory_order_release);
+    return 0;
+}
+
+template <typename T, int LOGB, bool NOCSUB>
+int launch_fast_fwd(GpuContext *ctx, const T *src, T *dst, unsigned grid, uint32_t limbs) {
+    static std::atomic<uint32_t> done{0};
+    constexpr size_t smem = gp::fast_smem_bytes<T, LOGB>();
+    auto kernel = gp::fast_ntt_fwd_kernel<T, LOGB, NOCSUB>;
+    if (optin_smem(kernel, smem, ctx->device, done)) return 1;
+    kernel<<<grid, gp::FastCfg<T, LOGB>::kThreads, smem, ctx->stream>>>(src, dst, limbs, (uint32_t)ctx->logN,
+                                                                       (const gp::TwPair<T> *)ctx->d_fwd,
+                                                                       (const gp::LimbConst<T> *)ctx->d_limb);
+    gp::count_launch();
+    GP_CHECK_LAUNCH("fast_ntt_fwd_kernel");
+    return 0;
+}
+template <typename T, int LOGB>
+int launch_fast_inv(GpuContext *ctx, const T *src, T *dst, unsigned grid, uint32_t limbs) {
+    static std::atomic<uint32_t> done{0};
+    constexpr size_t smem = gp::fast_smem_bytes<T, LOGB>();
+    auto kernel = gp::fast_ntt_inv_kernel<T, LOGB>;
+    if (optin_smem(kernel, smem, ctx->device, done)) return 1;
+    kernel<<<grid, gp::FastCfg<T, LOGB>::kThreads, smem, ctx->stream>>>(src, dst, limbs, (uint32_t)ctx->logN,
+                                                                       (const gp::TwPair<T> *)ctx->d_inv,
+                                                                       (const gp::LimbConst<T> *)ctx->d_limb);
+    gp::count_launch();
+    GP_CHECK_LAUNCH("fast_ntt_inv_kernel");
+    return 0;
+}
+#define GP_FAST_LOGB_SWITCH(logb, CALL)                                   \
+    switch (logb) {                                                       \
+        case 12: return CALL(12);                                         \
+        case 13: return CALL(13);                                         \
+        case 14: return CALL(14);                                         \
+        case 15:                                                          \
+            if constexpr (sizeof(T) == 4) return CALL(15);                \
+            [[fallthrough]];                                              \
+        default: return gp::set_error("no compile-time NTT plan for this block size"); \
+    }
+template <typename T> int dispatch_fast_fwd(GpuContext *ctx, const T *src, T *dst, unsigned grid, uint32_t limbs, int logb) {
+#define GP_CALL(LB) (ctx->nocsub ? launch_fast_fwd<T, LB, true>(ctx, src, dst, grid, limbs) : launch_fast_fwd<T, LB, false>(ctx, src, dst, grid, limbs))
+    GP_FAST_LOGB_SWITCH(logb, GP_CALL)
+#undef GP_CALL
+}
+template <typename T> int dispatch_fast_inv(GpuContext *ctx, const T *src, T *dst, unsigned grid, uint32_t limbs, int logb) {
+#define GP_CALL(LB) launch_fast_inv<T, LB>(ctx, src, dst, grid, limbs)
+    GP_FAST_LOGB_SWITCH(logb, GP_CALL)
+#undef GP_CALL
+}
 
 template <typename T> int ensure_ntt_smem(GpuContext *ctx, size_t bytes) {
     // opt in to > 48 KB dynamic shared memory once per context and kernel family
@@ -71,8 +137,9 @@ template <typename T> int run_ntt_fwd(GpuContext *ctx, const T *src, T *dst, siz
     const size_t pl = polys * limbs;
     if (pl == 0) return 0;
     const int logn = ctx->logN, logb = ntt_block_log<T>(ctx), top = logn - logb;
+    const bool fast = use_fast<T>(ctx, logb);
     const size_t smem = gp::ntt_smem_bytes<T>(logb);
-    if (ensure_ntt_smem<T>(ctx, smem)) return 1;
+    if (!fast && ensure_ntt_smem<T>(ctx, smem)) return 1;
     if (top > 0) {
         if (src != dst)
             GP_CUDA(cudaMemcpyAsync(dst, src, (pl << logn) * sizeof(T), cudaMemcpyDeviceToDevice, ctx->stream), "cudaMemcpyAsync(ntt)");
@@ -86,6 +153,7 @@ template <typename T> int run_ntt_fwd(GpuContext *ctx, const T *src, T *dst, siz
         }
     }
     const unsigned grid = (unsigned)(pl << top);
+    if (fast) return dispatch_fast_fwd<T>(ctx, src, dst, grid, limbs, logb);
     gp::ntt_fwd_kernel<T><<<grid, gp::NttCfg<T>::kThreads, smem, ctx->stream>>>(
         src, dst, limbs, (uint32_t)logn, (uint32_t)logb, (const gp::TwPair<T> *)ctx->d_fwd, (const gp::LimbConst<T> *)ctx->d_limb);
     gp::count_launch();
@@ -97,13 +165,18 @@ template <typename T> int run_ntt_inv(GpuContext *ctx, const T *src, T *dst, siz
     const size_t pl = polys * limbs;
     if (pl == 0) return 0;
     const int logn = ctx->logN, logb = ntt_block_log<T>(ctx), top = logn - logb;
+    const bool fast = use_fast<T>(ctx, logb);
     const size_t smem = gp::ntt_smem_bytes<T>(logb);
-    if (ensure_ntt_smem<T>(ctx, smem)) return 1;
     const unsigned grid = (unsigned)(pl << top);
-    gp::ntt_inv_kernel<T><<<grid, gp::NttCfg<T>::kThreads, smem, ctx->stream>>>(
-        src, dst, limbs, (uint32_t)logn, (uint32_t)logb, (const gp::TwPair<T> *)ctx->d_inv, (const gp::LimbConst<T> *)ctx->d_limb);
-    gp::count_launch();
-    GP_CHECK_LAUNCH("ntt_inv_kernel");
+    if (fast) {
+        if (dispatch_fast_inv<T>(ctx, src, dst, grid, limbs, logb)) return 1;
+    } else {
+        if (ensure_ntt_smem<T>(ctx, smem)) return 1;
+        gp::ntt_inv_kernel<T><<<grid, gp::NttCfg<T>::kThreads, smem, ctx->stream>>>(
+            src, dst, limbs, (uint32_t)logn, (uint32_t)logb, (const gp::TwPair<T> *)ctx->d_inv, (const gp::LimbConst<T> *)ctx->d_limb);
+        gp::count_launch();
+        GP_CHECK_LAUNCH("ntt_inv_kernel");
+    }
     if (top > 0) {
         int passes[8], np = 0;
         split_top(top, passes, &np);

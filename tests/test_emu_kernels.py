@@ -74,6 +74,25 @@ CASES = [
     (4096, 2, 51, 7, 0),
     (512, 1, 51, 8, 0),
     (256, 1, 24, 1, 0),
+    # compile-time-planned kernels (ntt_fast.cuh): NOCSUB (24/26-bit, 51-bit) and csub (28/29-bit, 61-bit)
+    (4096, 2, 24, 0, 0),
+    (4096, 1, 29, 0, 0),
+    (8192, 1, 26, 0, 0),
+    (8192, 1, 28, 0, 0),
+    (16384, 2, 24, 0, 0),
+    (16384, 1, 29, 0, 0),
+    (32768, 1, 24, 0, 0),
+    (32768, 1, 28, 0, 0),
+    (65536, 1, 24, 0, 0),   # 2^14 blocks under a radix-4 global pass
+    (65536, 1, 29, 0, 0),
+    (4096, 1, 51, 0, 0),
+    (8192, 1, 61, 0, 0),
+    (16384, 1, 51, 0, 0),
+    (16384, 1, 61, 0, 0),
+    (32768, 1, 51, 0, 0),   # 2^13 blocks under a radix-4 global pass
+    (65536, 1, 61, 0, 0),
+    (16384, 1, 24, 0, 1),   # u64 storage forced for a small modulus
+    (16384, 1, 24, 14, 0),  # same ring through the generic kernel
 ]
 
 
@@ -93,7 +112,7 @@ def test_emu_ntt_matches_oracle(emu, n, depth, bits, cap, fw):
 
 def test_emu_ntt_extreme_values(emu):
     """all coefficients q-1 (largest lazy values) and all zero"""
-    for n, depth, bits in [(4096, 2, 29), (1024, 2, 61), (1024, 2, 51)]:
+    for n, depth, bits in [(4096, 2, 29), (1024, 2, 61), (1024, 2, 51), (16384, 1, 26), (16384, 1, 29), (16384, 1, 57), (16384, 1, 61)]:
         pl = plan(n, depth, bits)
         mod = np.array(pl.moduli, dtype=np.uint64)
         a = np.empty((1, 2, depth, n), dtype=np.uint64)
@@ -120,6 +139,10 @@ DEC_CASES = [
     (256, 3, 24, 12, 1, 0),
     (512, 2, 28, 14, 0, 5),
     (64, 2, 51, 20, 1, 0),
+    (4096, 2, 24, 12, 0, 0),   # fast fused digit + NTT kernels
+    (8192, 1, 28, 14, 0, 0),
+    (4096, 1, 51, 17, 0, 0),
+    (4096, 2, 24, 12, 1, 0),
 ]
 
 
