@@ -188,7 +188,7 @@ def make_params(cfg, device):
     return GpuDCRTPolyParams(cfg["n"], moduli, cfg.get("bb", 12), gpu_ids=(device,)), moduli
 
 
-def bench_ntt(device, steps, warmup, hbm_peak):
+def bench_ntt(device, steps, warmup, hbm_peak, ip=None):
     """configs[1]: batched NTT -> INTT round trips; Gcoeff/s per direction against the HBM roofline."""
     from mxx_b200 import GpuDCRTPolyMatrix, ffi
 
@@ -221,7 +221,16 @@ def bench_ntt(device, steps, warmup, hbm_peak):
         coeffs = P * depth * n
         algo_bytes = 2 * (2 * W * coeffs)  # one read + one write per coefficient, two directions
         gbs = algo_bytes / (ms * 1e-3) / 1e9
-        out.append({"n": n, "limbs": depth, "crt_bits": bits, "word_bytes": W, "polys": P, "ms_roundtrip": round(ms, 4),
+        bfly_s = 2 * coeffs / 2 * (n.bit_length() - 1) / (ms * 1e-3)
+        int_roof = None
+        if ip and "bfly_fwd_u32" in ip:
+            # a round trip is one forward + one inverse transform: harmonic mean of the two measured butterfly peaks
+            kf = ("bfly_fwd_u32_nocsub" if max(moduli) * 36 < (1 << 32) else "bfly_fwd_u32") if W == 4 else "bfly_fwd_u64_nocsub"
+            ki = "bfly_inv_u32" if W == 4 else "bfly_inv_u64"
+            peak = 2.0 / (1.0 / ip[kf] + 1.0 / ip[ki])
+            int_roof = {"bound": "int-issue", "achieved": round(bfly_s, 0), "peak": round(peak, 0), "unit": "butterflies/s",
+                        "frac": round(bfly_s / peak, 4), "peak_source": "tools/modmul_peak.cu run in this process' box (register-resident butterflies)"}
+        out.append({"n": n, "limbs": depth, "crt_bits": bits, "word_bytes": W, "polys": P, "ms_roundtrip": round(ms, 4), "int_roofline": int_roof,
                     "gcoeff_per_s_per_direction": round(2 * coeffs / (ms * 1e-3) / 1e9, 2),
                     "butterflies_per_s": round(2 * coeffs / 2 * (n.bit_length() - 1) / (ms * 1e-3), 0),
                     "roofline": {"bound": "hbm", "achieved": round(gbs, 1), "peak": hbm_peak, "unit": "GB/s",
@@ -233,7 +242,7 @@ def bench_ntt(device, steps, warmup, hbm_peak):
     return out
 
 
-def bench_mul_decompose(device, steps, warmup, hbm_peak):
+def bench_mul_decompose(device, steps, warmup, hbm_peak, ip=None):
     """configs[2] (C3-a): S(1x30) * G^-1(other 1x30), n=2^14, 15x24-bit limbs, base 2^12."""
     from mxx_b200 import GpuDCRTPolyMatrix, ffi
 
@@ -265,10 +274,72 @@ def bench_mul_decompose(device, steps, warmup, hbm_peak):
     butterflies = (cfg["d"] * cfg["c"] * Lm + m_in * cfg["c"] * Lm) * (n // 2) * logn
     macs = cfg["r"] * m_in * cfg["c"] * Lm * n
     min_bytes = W * Lm * n * (cfg["r"] * m_in + cfg["d"] * cfg["c"] + cfg["r"] * cfg["c"])
-    return {"workload": "C3-a mul_decompose S(1x30)*G^-1(1x30) n=2^14 L=15x24-bit bb=12", "ms_fused": round(ms, 4),
-            "mul_decompose_per_s": round(1e3 / ms, 2), "ms_reference_call_sequence": round(seq_ms, 3),
-            "modmul_per_s": round((butterflies + macs) / (ms * 1e-3), 0), "butterflies": butterflies, "macs": macs,
-            "min_hbm_bytes": min_bytes, "hbm_frac_of_min_bytes": round(min_bytes / (ms * 1e-3) / 1e9 / hbm_peak, 4)}
+    res = {"workload": "C3-a mul_decompose S(1x30)*G^-1(1x30) n=2^14 L=15x24-bit bb=12", "ms_fused": round(ms, 4),
+           "mul_decompose_per_s": round(1e3 / ms, 2), "ms_reference_call_sequence": round(seq_ms, 3),
+           "modmul_per_s": round((butterflies + macs) / (ms * 1e-3), 0), "butterflies": butterflies, "macs": macs,
+           "min_hbm_bytes": min_bytes, "hbm_frac_of_min_bytes": round(min_bytes / (ms * 1e-3) / 1e9 / hbm_peak, 4)}
+    if ip and "bfly_fwd_u32_nocsub" in ip:
+        fwd_b = m_in * cfg["c"] * Lm * (n // 2) * logn
+        inv_b = cfg["d"] * cfg["c"] * Lm * (n // 2) * logn
+        ideal_s = fwd_b / ip["bfly_fwd_u32_nocsub"] + inv_b / ip["bfly_inv_u32"] + macs / ip["mac_u32"]
+        res["int_roofline"] = {"bound": "int-issue", "ideal_ms": round(ideal_s * 1e3, 4), "frac": round(ideal_s / (ms * 1e-3), 4),
+                               "how": "butterflies / measured butterfly peak + MACs / measured MAC peak (tools/modmul_peak.cu), divided by the measured time"}
+    # CPU baseline on a bounded sample (2 of the 30 columns), all host threads, and a parity check of those columns
+    from oracle import oracle as orc
+
+    plan = orc.Plan(n, moduli)
+    t0 = time.perf_counter()
+    cpu = plan.mul_decompose(S, O[:, :2], cfg["bb"])
+    dt = time.perf_counter() - t0
+    assert np.array_equal(cpu, out.to_rns()[:, :2]), "GPU mul_decompose differs from the CPU oracle"
+    res["cpu_baseline"] = {"value": round(1.0 / (dt * cfg["c"] / 2), 4), "unit": "mul_decompose/s", "cores": orc.lib().orc_get_threads(),
+                           "kind": "port", "sample": "2 of the 30 columns (oracle/dcrt_oracle.c orc_mul_decompose), scaled by 15",
+                           "parity": "bit-exact vs GPU result on the sampled columns"}
+    return res
+
+
+def int_peaks():
+    """Register-resident microbenchmark of the butterfly / MAC primitives (tools/modmul_peak.cu): the measured
+    INT-issue roofline denominators (butterflies/s, MACs/s) for the compute-bound kernels."""
+    exe = os.path.join(ROOT, "mxx_b200", "modmul_peak")
+    if not os.path.exists(exe):
+        return None
+    try:
+        out = subprocess.run([exe], capture_output=True, text=True, timeout=120).stdout.strip().splitlines()[-1]
+        return json.loads(out)
+    except Exception as e:  # the roofline then only has its HBM leg
+        return {"error": repr(e)}
+
+
+def bench_reference_gpu(cfg, pinA, pinB, moduli, want):
+    """The reference's own `gpu` feature path (its CUDA library compiled unmodified into oracle/_ref/)
+    on the same operands, WITH a device sync before the clock is read (its bench has none,
+    benches/bench_matrix_mul_gpu.rs:31-36).  A baseline beside the number, never part of the product path."""
+    path = os.path.join(ROOT, "oracle", "_ref", "libgpupoly_ref.so")
+    if not os.path.exists(path):
+        return {"unavailable": "oracle/_ref/libgpupoly_ref.so not built"}
+    from mxx_b200 import GpuDCRTPolyMatrix, GpuDCRTPolyParams, ffi
+
+    try:
+        lib = ffi.bind(path, extensions=False)
+        params = GpuDCRTPolyParams(cfg["n"], moduli, cfg["bb"], library=lib)
+        gA = GpuDCRTPolyMatrix.from_rns(params, pinA, True)
+        gB = GpuDCRTPolyMatrix.from_rns(params, pinB, True)
+        lib.gpu_device_synchronize()
+        times = []
+        out = None
+        for _ in range(3):
+            t0 = time.perf_counter()
+            out = gA * gB
+            ffi.check_status(lib.gpu_device_synchronize(), "gpu_device_synchronize", lib)
+            times.append(time.perf_counter() - t0)
+        same = bool(np.array_equal(out.to_rns(), want))
+        dt = min(times)
+        return {"value": round(1.0 / dt, 3), "unit": "matrix-muls/s", "ms_per_step": round(dt * 1e3, 3), "kind": "reference",
+                "how": "cuda/ of the reference compiled for sm_100 (oracle/Makefile), gpu_matrix_mul + gpu_device_synchronize, best of 3",
+                "same_result_as_ours": same}
+    except Exception as e:
+        return {"unavailable": repr(e)[:200]}
 
 
 def cpu_matmul_baseline(A, B, moduli, n, reps):
@@ -298,8 +369,10 @@ def run_gpu(args):
 
     # synthetic operands, generated straight into pinned host memory (the e2e leg copies from there)
     pinA, pinB, pinO = PinnedBuffer((r, k, Lm, n)), PinnedBuffer((k, c, Lm, n)), PinnedBuffer((r, c, Lm, n))
-    uniform_host(pinA.array, moduli, seed=0x6D7878_0001 + 2 * dist.rank)
-    uniform_host(pinB.array, moduli, seed=0x6D7878_0001 + 2 * dist.rank + 1)
+    # column-block sharding: the job is A(1x30) * B(30 x 120*N); A is replicated (same seed on every rank),
+    # rank g owns columns [120 g, 120 (g+1)) of B and of the result.  No collective in the data path.
+    uniform_host(pinA.array, moduli, seed=0x6D7878_0001)
+    uniform_host(pinB.array, moduli, seed=0x6D7878_0100 + dist.rank)
     gA, gB = GpuDCRTPolyMatrix(params, r, k), GpuDCRTPolyMatrix(params, k, c)
     gO = GpuDCRTPolyMatrix(params, r, c)
     gA.load_rns(pinA.array, GPU_POLY_FORMAT_EVAL)
@@ -340,13 +413,31 @@ def run_gpu(args):
     e2e_value = dist.world * e2e_steps / e2e_s
     result_host = pinO.array.copy()
 
+    # ---- assembly (N > 1): one NCCL all-gather of the ranks' output column blocks, timed on its own -------------
+    assemble = None
+    if dist.world > 1:
+        from mxx_b200.dist import ColumnShardedOps
+
+        ops = ColumnShardedOps(params)
+        ops.all_gather_columns(gO, c * dist.world)  # warm-up (NCCL communicator setup)
+        params.synchronize()
+        dist.barrier()
+        t0 = time.perf_counter()
+        full = ops.all_gather_columns(gO, c * dist.world)
+        params.synchronize()
+        asm_s = dist.max(time.perf_counter() - t0)
+        nbytes = r * c * dist.world * Lm * n * 4
+        assemble = {"ms": round(asm_s * 1e3, 3), "bytes_assembled_per_rank": nbytes,
+                    "what": "all_gather of the r x 120 output blocks into the r x 120N result on every rank (mxx_b200/dist.py); not part of `value`"}
+        del full
+
     line = {
         "metric": "DCRT matrix-muls/s", "value": round(value, 2), "unit": "matrix-muls/s", "n_gpus": dist.world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
         "config": {"workload": "C1-R bench_matrix_mul: DCRTPolyMatrix 1x30 * 30x120, n=2^14, 15 CRT limbs x 24 bit, EVAL operands "
                                "(benches/bench_matrix_mul_cpu.rs:10-16)", "ring_dim": n, "limbs": Lm, "crt_bits": cfg["bits"],
-                   "shape": [r, k, c], "per_gpu": "one independent product per rank", "l2": "inputs (3.57 GB) exceed the 126 MB L2"},
+                   "shape": [r, k, c], "per_gpu": "column block: A 1x30 replicated, each rank owns 120 columns of B and of the result (job = 1x30 * 30x(120*N)); value counts 120-column products", "l2": "inputs (3.57 GB) exceed the 126 MB L2"},
         "e2e": {"value": round(e2e_value, 3), "unit": "matrix-muls/s", "h2d_bytes_per_step": int(pinA.nbytes + pinB.nbytes),
                 "d2h_bytes_per_step": int(pinO.nbytes), "steps": e2e_steps,
                 "path": "gpu_matrix_load_rns_batch x2 (pinned host u64) -> gpu_matrix_mul -> gpu_matrix_store_rns_batch -> gpu_event_set_wait"},
@@ -356,6 +447,8 @@ def run_gpu(args):
                      "peak_source": peak_src},
         "clocks": clk.summary(),
     }
+    if assemble:
+        line["assemble"] = assemble
 
     if dist.rank == 0 and dist.world == 1:
         # CPU baseline beside it: same operands, all host threads, and a parity check of the GPU result
@@ -367,10 +460,15 @@ def run_gpu(args):
                                     "sample": f"the full C1-R product x{reps} (oracle/dcrt_oracle.c orc_matrix_mul, OpenMP)",
                                     "parity": "bit-exact vs GPU result"}
         del gA, gB, gO
+        if not args.no_cpu:
+            params.synchronize()
+            line["reference_gpu"] = bench_reference_gpu(cfg, pinA.array, pinB.array, moduli, result_host)
         pinB.free()
         if not args.no_extras:
-            line["ntt"] = bench_ntt(device, max(3, min(args.steps, 20)), args.warmup, hbm_peak)
-            line["mul_decompose"] = bench_mul_decompose(device, max(3, min(args.steps, 20)), args.warmup, hbm_peak)
+            ip = int_peaks()
+            line["int_peaks"] = ip
+            line["ntt"] = bench_ntt(device, max(3, min(args.steps, 20)), args.warmup, hbm_peak, ip)
+            line["mul_decompose"] = bench_mul_decompose(device, max(3, min(args.steps, 20)), args.warmup, hbm_peak, ip)
     if dist.rank == 0:
         print(json.dumps(line), flush=True)
     dist.close()

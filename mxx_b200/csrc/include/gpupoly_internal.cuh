@@ -29,6 +29,14 @@ int set_error(const std::string &msg);
 int set_cuda_error(cudaError_t err, const char *where);
 extern std::atomic<uint64_t> g_launches;
 inline void count_launch(uint64_t n = 1) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+// Stream the launch helpers use: the context stream unless the calling thread has scoped an
+// override (a context is shared by many host threads, so the override is thread-local).
+extern thread_local cudaStream_t tl_stream;
+struct StreamScope {
+    cudaStream_t prev;
+    explicit StreamScope(cudaStream_t s) : prev(tl_stream) { tl_stream = s; }
+    ~StreamScope() { tl_stream = prev; }
+};
 }  // namespace gp
 
 #define GP_CUDA(call, where)                                         \
@@ -49,6 +57,10 @@ struct GpuContext {
     bool wide = false;       // true: u64 storage, false: u32 storage
     uint32_t crt_bits = 0;   // widest modulus
     cudaStream_t stream = nullptr;
+    // two auxiliary streams + events: independent column chunks of mul_decompose run on them so
+    // that one chunk's tail wave overlaps the next chunk's kernels (MatrixDecompose.inl)
+    cudaStream_t aux[2] = {nullptr, nullptr};
+    cudaEvent_t ev_fork = nullptr, ev_join[2] = {nullptr, nullptr};
     int sm_count = 0;
     int max_smem_optin = 0;
     // device tables; element type follows `wide`
@@ -61,6 +73,10 @@ struct GpuContext {
     uint32_t mac_fold = 1;   // products that fit one lazy accumulator between folds
     size_t word_bytes() const { return wide ? 8 : 4; }
 };
+
+namespace gp {
+inline cudaStream_t cur(const GpuContext *ctx) { return tl_stream ? tl_stream : ctx->stream; }
+}  // namespace gp
 
 struct GpuMatrix {
     GpuContext *ctx = nullptr;

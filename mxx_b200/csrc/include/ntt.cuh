@@ -39,6 +39,7 @@ template <typename T> inline size_t ntt_smem_bytes(int logb) {
 // Source functors: logical coefficient index -> value in [0, 4q).
 template <typename T> struct PlainSrc {
     const T *p;
+    GP_HD T xform(T raw) const { return raw; }
     GP_HD T operator()(uint32_t i) const { return p[i]; }
 };
 // Gadget digit of a coefficient-form residue, the fused load of decompose + NTT:
@@ -49,10 +50,11 @@ template <typename T> struct DigitSrc {
     uint32_t shift;
     T mask;
     T q;
-    GP_HD T operator()(uint32_t i) const {
-        T d = (p[i] >> shift) & mask;
+    GP_HD T xform(T raw) const {
+        T d = (raw >> shift) & mask;
         return d >= q ? d % q : d;
     }
+    GP_HD T operator()(uint32_t i) const { return xform(p[i]); }
 };
 
 // ---- register butterfly networks ------------------------------------------------

@@ -70,6 +70,67 @@ template <int LOGB> struct SmemView<uint64_t, LOGB> {
     }
 };
 
+
+// launch shape per block size (needed by the passes: loop trip counts are compile-time constants)
+template <typename T, int LOGB> struct FastCfg {
+    static constexpr bool kSmall = fast_smem_bytes<T, LOGB>() <= 72 * 1024;  // three blocks per SM
+#ifndef GP_FAST_THREADS
+#define GP_FAST_THREADS 256
+#endif
+#ifndef GP_FAST_MINB
+#define GP_FAST_MINB 3
+#endif
+    static constexpr int kThreads = kSmall ? GP_FAST_THREADS : 512;
+    static constexpr int kMinBlocks = kSmall ? (sizeof(T) == 4 ? GP_FAST_MINB : 2) : 1;
+};
+
+// ---- asynchronous global -> shared staging (LDGSTS) ---------------------------------------------
+// A thread stages exactly the words it will consume itself, so cp.async.wait_group is the only
+// synchronisation needed; all of a CTA's global loads are in flight within its first few hundred
+// cycles and no register is tied up while they travel.
+#ifndef GP_NTT_ASYNC
+#define GP_NTT_ASYNC 1
+#endif
+#ifndef GP_NTT_ASYNC_FWD
+#define GP_NTT_ASYNC_FWD 0
+#endif
+#ifndef GP_NTT_ASYNC_INV
+#define GP_NTT_ASYNC_INV 1
+#endif
+#ifndef GP_FLAST_U
+#define GP_FLAST_U 2
+#endif
+#if defined(__CUDA_ARCH__) && GP_NTT_ASYNC
+#define GP_ASYNC_STAGE 1
+__device__ __forceinline__ void cp_async4(void *smem_dst, const void *gsrc) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gsrc) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait(int pending) {
+    switch (pending) {
+        case 0: asm volatile("cp.async.wait_group 0;" ::: "memory"); break;
+        case 1: asm volatile("cp.async.wait_group 1;" ::: "memory"); break;
+        case 2: asm volatile("cp.async.wait_group 2;" ::: "memory"); break;
+        case 3: asm volatile("cp.async.wait_group 3;" ::: "memory"); break;
+        case 4: asm volatile("cp.async.wait_group 4;" ::: "memory"); break;
+        case 5: asm volatile("cp.async.wait_group 5;" ::: "memory"); break;
+        case 6: asm volatile("cp.async.wait_group 6;" ::: "memory"); break;
+        default: asm volatile("cp.async.wait_group 7;" ::: "memory"); break;
+    }
+}
+// warm the L2 with the block a CTA started one residency period later will read
+__device__ __forceinline__ void prefetch_l2(const void *p, unsigned bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
+#else
+#define GP_ASYNC_STAGE 0
+#endif
+
 // 4 consecutive words from / to global memory (16 bytes for u32, 32 bytes for u64)
 GP_HD void gld4(const uint32_t *p, uint32_t (&x)[4]) {
     const uint4 v = *reinterpret_cast<const uint4 *>(p);
@@ -93,60 +154,128 @@ template <typename T> GP_HD T csub_min(T x, T m) {
 // any word -> [0, 2q): Shoup multiplication by one, one_s = floor(2^wordbits / q)
 template <typename T> GP_HD T reduce_lazy(T x, T one_s, T q) { return x - mulhi(x, one_s) * q; }
 
+
+// COUNT consecutive twiddle pairs starting at an index that is a multiple of COUNT: 128-bit loads
+#ifndef GP_TW_VEC
+#define GP_TW_VEC 1
+#endif
+template <int COUNT> GP_HD void load_tw(const TwPair<uint32_t> *__restrict__ p, TwPair<uint32_t> (&w)[COUNT]) {
+    if constexpr (COUNT >= 2 && GP_TW_VEC) {
+#pragma unroll
+        for (int i = 0; i < COUNT / 2; i++) {
+            const uint4 v = reinterpret_cast<const uint4 *>(p)[i];
+            w[2 * i].w = v.x, w[2 * i].ws = v.y, w[2 * i + 1].w = v.z, w[2 * i + 1].ws = v.w;
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < COUNT; i++) w[i] = p[i];
+    }
+}
+template <int COUNT> GP_HD void load_tw(const TwPair<uint64_t> *__restrict__ p, TwPair<uint64_t> (&w)[COUNT]) {
+#pragma unroll
+    for (int i = 0; i < COUNT; i++) w[i] = p[i];
+}
+
 // ---- butterfly networks ---------------------------------------------------------------------
 // Forward (Cooley-Tukey): stage s pairs j and j + (R >> (s+1)); twiddle index (twbase << s) + u.
 // NOCSUB: inputs < B give outputs < B + 2q*LOGR; otherwise values stay in [0, 4q).
-template <typename T, int LOGR, bool NOCSUB>
-GP_HD void fwd_net(T (&x)[1 << LOGR], const TwPair<T> *__restrict__ tw, uint32_t twbase, T q, T q2) {
-    constexpr int R = 1 << LOGR;
+template <typename T, int LOGR, int S, bool NOCSUB>
+GP_HD void fwd_stage(T (&x)[1 << LOGR], const TwPair<T> *__restrict__ tw, uint32_t twbase, T q, T q2) {
+    constexpr int R = 1 << LOGR, half = R >> (S + 1), cnt = 1 << S;
+    TwPair<T> w[cnt];
+    load_tw<cnt>(tw + ((size_t)twbase << S), w);
 #pragma unroll
-    for (int s = 0; s < LOGR; s++) {
-        const int half = R >> (s + 1);
+    for (int u = 0; u < cnt; u++) {
 #pragma unroll
-        for (int u = 0; u < (1 << s); u++) {
-            const TwPair<T> w = tw[(twbase << s) + u];
-#pragma unroll
-            for (int v = 0; v < half; v++) {
-                const int j0 = u * 2 * half + v, j1 = j0 + half;
-                const T X = NOCSUB ? x[j0] : csub_min<T>(x[j0], q2);
-                const T t = mul_shoup_lazy<T>(x[j1], w.w, w.ws, q);
-                x[j0] = X + t;
-                x[j1] = X - t + q2;
-            }
+        for (int v = 0; v < half; v++) {
+            const int j0 = u * 2 * half + v, j1 = j0 + half;
+            const T X = NOCSUB ? x[j0] : csub_min<T>(x[j0], q2);
+            const T t = mul_shoup_lazy<T>(x[j1], w[u].w, w[u].ws, q);
+            x[j0] = X + t;
+            x[j1] = X - t + q2;
         }
     }
+    if constexpr (S + 1 < LOGR) fwd_stage<T, LOGR, S + 1, NOCSUB>(x, tw, twbase, q, q2);
+}
+template <typename T, int LOGR, bool NOCSUB>
+GP_HD void fwd_net(T (&x)[1 << LOGR], const TwPair<T> *__restrict__ tw, uint32_t twbase, T q, T q2) {
+    fwd_stage<T, LOGR, 0, NOCSUB>(x, tw, twbase, q, q2);
 }
 // Inverse (Gentleman-Sande): stage s pairs j and j + (1 << s); inputs and outputs in [0, 2q).
 // FINAL merges n^-1 (and n^-1 * last twiddle) into the last stage.
-template <typename T, int LOGR, bool FINAL>
-GP_HD void inv_net(T (&x)[1 << LOGR], const TwPair<T> *__restrict__ tw, uint32_t twbase, const LimbConst<T> &c) {
-    constexpr int R = 1 << LOGR;
+template <typename T, int LOGR, int S, bool FINAL>
+GP_HD void inv_stage(T (&x)[1 << LOGR], const TwPair<T> *__restrict__ tw, uint32_t twbase, const LimbConst<T> &c) {
+    constexpr int R = 1 << LOGR, groups = R >> (S + 1);
     const T q = c.q, q2 = c.q2;
+    if constexpr (FINAL && S == LOGR - 1) {
 #pragma unroll
-    for (int s = 0; s < LOGR; s++) {
-        const int groups = R >> (s + 1);
+        for (int v = 0; v < (1 << S); v++) {
+            const int j0 = v, j1 = j0 + (1 << S);
+            const T X = x[j0], Y = x[j1];
+            x[j0] = mul_shoup_lazy<T>(X + Y, c.ninv, c.ninv_s, q);
+            x[j1] = mul_shoup_lazy<T>(X - Y + q2, c.nw, c.nw_s, q);
+        }
+    } else {
+        TwPair<T> w[groups];
+        load_tw<groups>(tw + (size_t)twbase * groups, w);
 #pragma unroll
         for (int u = 0; u < groups; u++) {
-            if (FINAL && s == LOGR - 1) {
 #pragma unroll
-                for (int v = 0; v < (1 << s); v++) {
-                    const int j0 = u * (2 << s) + v, j1 = j0 + (1 << s);
-                    const T X = x[j0], Y = x[j1];
-                    x[j0] = mul_shoup_lazy<T>(X + Y, c.ninv, c.ninv_s, q);
-                    x[j1] = mul_shoup_lazy<T>(X - Y + q2, c.nw, c.nw_s, q);
-                }
-            } else {
-                const TwPair<T> w = tw[twbase * groups + u];
-#pragma unroll
-                for (int v = 0; v < (1 << s); v++) {
-                    const int j0 = u * (2 << s) + v, j1 = j0 + (1 << s);
-                    const T X = x[j0], Y = x[j1];
-                    x[j0] = csub_min<T>(X + Y, q2);
-                    x[j1] = mul_shoup_lazy<T>(X - Y + q2, w.w, w.ws, q);
-                }
+            for (int v = 0; v < (1 << S); v++) {
+                const int j0 = u * (2 << S) + v, j1 = j0 + (1 << S);
+                const T X = x[j0], Y = x[j1];
+                x[j0] = csub_min<T>(X + Y, q2);
+                x[j1] = mul_shoup_lazy<T>(X - Y + q2, w[u].w, w[u].ws, q);
             }
         }
     }
+    if constexpr (S + 1 < LOGR) inv_stage<T, LOGR, S + 1, FINAL>(x, tw, twbase, c);
+}
+template <typename T, int LOGR, bool FINAL>
+GP_HD void inv_net(T (&x)[1 << LOGR], const TwPair<T> *__restrict__ tw, uint32_t twbase, const LimbConst<T> &c) {
+    inv_stage<T, LOGR, 0, FINAL>(x, tw, twbase, c);
+}
+
+// ---- radix-4 networks on 4 consecutive words with preloaded twiddles -------------------------------
+// The three twiddles of such a group are tw[tb], tw[2 tb], tw[2 tb + 1]: the last two are adjacent, so
+// they come in one 128-bit load (u32) and all of a thread's twiddle loads can be issued ahead of the data.
+template <typename T> struct Tw3 { TwPair<T> a, b0, b1; };
+GP_HD Tw3<uint32_t> load_tw3(const TwPair<uint32_t> *__restrict__ tw, uint32_t tb) {
+    Tw3<uint32_t> r;
+    r.a = tw[tb];
+    const uint4 v = *reinterpret_cast<const uint4 *>(tw + 2 * (size_t)tb);
+    r.b0.w = v.x, r.b0.ws = v.y, r.b1.w = v.z, r.b1.ws = v.w;
+    return r;
+}
+GP_HD Tw3<uint64_t> load_tw3(const TwPair<uint64_t> *__restrict__ tw, uint32_t tb) {
+    Tw3<uint64_t> r;
+    r.a = tw[tb];
+    r.b0 = tw[2 * (size_t)tb];
+    r.b1 = tw[2 * (size_t)tb + 1];
+    return r;
+}
+template <typename T, bool NOCSUB> GP_HD void fwd_bfly(T &x0, T &x1, const TwPair<T> &w, T q, T q2) {
+    const T X = NOCSUB ? x0 : csub_min<T>(x0, q2);
+    const T t = mul_shoup_lazy<T>(x1, w.w, w.ws, q);
+    x0 = X + t;
+    x1 = X - t + q2;
+}
+template <typename T, bool NOCSUB> GP_HD void fwd_net4(T (&x)[4], const Tw3<T> &t, T q, T q2) {
+    fwd_bfly<T, NOCSUB>(x[0], x[2], t.a, q, q2);
+    fwd_bfly<T, NOCSUB>(x[1], x[3], t.a, q, q2);
+    fwd_bfly<T, NOCSUB>(x[0], x[1], t.b0, q, q2);
+    fwd_bfly<T, NOCSUB>(x[2], x[3], t.b1, q, q2);
+}
+template <typename T> GP_HD void inv_bfly(T &x0, T &x1, const TwPair<T> &w, T q, T q2) {
+    const T X = x0, Y = x1;
+    x0 = csub_min<T>(X + Y, q2);
+    x1 = mul_shoup_lazy<T>(X - Y + q2, w.w, w.ws, q);
+}
+template <typename T> GP_HD void inv_net4(T (&x)[4], const Tw3<T> &t, T q, T q2) {
+    inv_bfly<T>(x[0], x[1], t.b0, q, q2);
+    inv_bfly<T>(x[2], x[3], t.b1, q, q2);
+    inv_bfly<T>(x[0], x[2], t.a, q, q2);
+    inv_bfly<T>(x[1], x[3], t.a, q, q2);
 }
 
 // ---- passes over one block of B = 2^LOGB words -------------------------------------------------
@@ -164,15 +293,42 @@ GP_HD void f_first(const Src &src, const SmemView<T, LOGB> &sm, const TwPair<T> 
                    T q, T q2) {
     constexpr int R1 = FastGeom<LOGB>::kR1, R = 1 << R1, LST = LOGB - R1;
     constexpr uint32_t stride = 1u << LST;
+#if GP_ASYNC_STAGE && GP_NTT_ASYNC_FWD
+    if constexpr (sizeof(T) == 4) {
+        constexpr int NT = FastCfg<T, LOGB>::kThreads, ITER = (int)(stride / NT);
+        static_assert(stride % NT == 0 && ITER >= 1 && ITER <= 8, "pass-1 staging plan");
+        const T *raw = src.p;
+#pragma unroll
+        for (int it = 0; it < ITER; it++) {
+            const uint32_t g = GP_TID + it * NT, base = padw(g);
+#pragma unroll
+            for (int j = 0; j < R; j++) cp_async4(sm.p + base + joff<LST>(j), raw + g + j * stride);
+            cp_async_commit();
+        }
+#pragma unroll
+        for (int it = 0; it < ITER; it++) {
+            cp_async_wait(ITER - 1 - it);
+            const uint32_t g = GP_TID + it * NT, base = padw(g);
+            T x[R];
+#pragma unroll
+            for (int j = 0; j < R; j++) x[j] = src.xform(sm.ld(base + joff<LST>(j)));
+            fwd_net<T, R1, NOCSUB>(x, tw, nblk + sb, q, q2);
+#pragma unroll
+            for (int j = 0; j < R; j++) sm.st(base + joff<LST>(j), x[j]);
+        }
+    } else
+#endif
+    {
 #pragma unroll 2
-    for (uint32_t g = GP_TID; g < stride; g += GP_NT) {
-        T x[R];
+        for (uint32_t g = GP_TID; g < stride; g += GP_NT) {
+            T x[R];
 #pragma unroll
-        for (int j = 0; j < R; j++) x[j] = src(g + j * stride);
-        fwd_net<T, R1, NOCSUB>(x, tw, nblk + sb, q, q2);
-        const uint32_t base = padw(g);
+            for (int j = 0; j < R; j++) x[j] = src(g + j * stride);
+            fwd_net<T, R1, NOCSUB>(x, tw, nblk + sb, q, q2);
+            const uint32_t base = padw(g);
 #pragma unroll
-        for (int j = 0; j < R; j++) sm.st(base + joff<LST>(j), x[j]);
+            for (int j = 0; j < R; j++) sm.st(base + joff<LST>(j), x[j]);
+        }
     }
 }
 // forward smem pass: radix 16 at stride 2^(LSPAN-4)
@@ -198,24 +354,33 @@ template <typename T, int LOGB, bool NOCSUB, int STAGES>
 GP_HD void f_last(const SmemView<T, LOGB> &sm, T *__restrict__ dst, const TwPair<T> *__restrict__ tw, uint32_t nblk, uint32_t sb,
                   const LimbConst<T> &c) {
     constexpr uint32_t groups = 1u << (LOGB - 2);
+    constexpr int U = sizeof(T) == 4 ? GP_FLAST_U : 2;  // groups whose twiddles are fetched ahead of the data
     const T q = c.q, q2 = c.q2;
-#pragma unroll 2
-    for (uint32_t g = GP_TID; g < groups; g += GP_NT) {
-        T x[4];
-        sm.ld4(4 * g + ((g >> 4) << 2), x);
-        fwd_net<T, 2, NOCSUB>(x, tw, ((nblk + sb) << (LOGB - 2)) + g, q, q2);
+    const uint32_t tb0 = (nblk + sb) << (LOGB - 2);
+#pragma unroll 1
+    for (uint32_t g0 = GP_TID; g0 < groups; g0 += U * GP_NT) {
+        Tw3<T> t[U];
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
-            T v = x[j];
-            if (NOCSUB) {
-                // < (1 + 2*STAGES) q: one Shoup-by-one brings it to [0, 2q)
-                v = reduce_lazy<T>(v, c.one_s, q);
-            } else {
-                v = csub_min<T>(v, q2);
+        for (int u = 0; u < U; u++) t[u] = load_tw3(tw, tb0 + g0 + u * GP_NT);
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const uint32_t g = g0 + u * GP_NT;
+            T x[4];
+            sm.ld4(4 * g + ((g >> 4) << 2), x);
+            fwd_net4<T, NOCSUB>(x, t[u], q, q2);
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                T v = x[j];
+                if (NOCSUB) {
+                    // < (1 + 2*STAGES) q: one Shoup-by-one brings it to [0, 2q)
+                    v = reduce_lazy<T>(v, c.one_s, q);
+                } else {
+                    v = csub_min<T>(v, q2);
+                }
+                x[j] = csub_min<T>(v, q);
             }
-            x[j] = csub_min<T>(v, q);
+            gst4(dst + 4 * g, x);
         }
-        gst4(dst + 4 * g, x);
     }
 }
 
@@ -224,12 +389,54 @@ template <typename T, int LOGB>
 GP_HD void i_first(const T *__restrict__ src, const SmemView<T, LOGB> &sm, const TwPair<T> *__restrict__ tw, uint32_t nblk,
                    uint32_t sb, const LimbConst<T> &c) {
     constexpr uint32_t groups = 1u << (LOGB - 2);
-#pragma unroll 2
-    for (uint32_t g = GP_TID; g < groups; g += GP_NT) {
-        T x[4];
-        gld4(src + 4 * g, x);
-        inv_net<T, 2, false>(x, tw, ((nblk + sb) << (LOGB - 2)) + g, c);
-        sm.st4(4 * g + ((g >> 4) << 2), x);
+#if GP_ASYNC_STAGE && GP_NTT_ASYNC_INV
+    if constexpr (sizeof(T) == 4) {
+        constexpr int NT = FastCfg<T, LOGB>::kThreads, ITER = (int)(groups / NT), BATCH = 4, NB = ITER / BATCH;
+        static_assert(groups % NT == 0 && ITER % BATCH == 0 && NB >= 1 && NB <= 8, "inverse pass-1 staging plan");
+#pragma unroll
+        for (int b = 0; b < NB; b++) {
+#pragma unroll
+            for (int i = 0; i < BATCH; i++) {
+                const uint32_t g = GP_TID + (b * BATCH + i) * NT;
+                cp_async16(sm.p + 4 * g + ((g >> 4) << 2), src + 4 * g);
+            }
+            cp_async_commit();
+        }
+#pragma unroll
+        for (int b = 0; b < NB; b++) {
+            Tw3<T> t[BATCH];
+#pragma unroll
+            for (int i = 0; i < BATCH; i++) t[i] = load_tw3(tw, ((nblk + sb) << (LOGB - 2)) + GP_TID + (b * BATCH + i) * NT);
+            cp_async_wait(NB - 1 - b);
+#pragma unroll
+            for (int i = 0; i < BATCH; i++) {
+                const uint32_t g = GP_TID + (b * BATCH + i) * NT, at = 4 * g + ((g >> 4) << 2);
+                T x[4];
+                sm.ld4(at, x);
+                inv_net4<T>(x, t[i], c.q, c.q2);
+                sm.st4(at, x);
+            }
+        }
+    } else
+#endif
+    {
+        constexpr int U = 2;
+#pragma unroll 1
+        for (uint32_t g0 = GP_TID; g0 < groups; g0 += U * GP_NT) {
+            Tw3<T> t[U];
+            T x[U][4];
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                t[u] = load_tw3(tw, ((nblk + sb) << (LOGB - 2)) + g0 + u * GP_NT);
+                gld4(src + 4 * (g0 + u * GP_NT), x[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const uint32_t g = g0 + u * GP_NT;
+                inv_net4<T>(x[u], t[u], c.q, c.q2);
+                sm.st4(4 * g + ((g >> 4) << 2), x[u]);
+            }
+        }
     }
 }
 // inverse smem pass: radix 16 at distance t0 = 2^LT0 (block span 2^(LT0+4))
@@ -318,11 +525,6 @@ GP_HD void fast_inv_block(const T *__restrict__ src, T *__restrict__ dst, void *
 }
 
 // ---- kernels ------------------------------------------------------------------------------------------
-template <typename T, int LOGB> struct FastCfg {
-    static constexpr bool kSmall = fast_smem_bytes<T, LOGB>() <= 72 * 1024;  // three blocks per SM
-    static constexpr int kThreads = kSmall ? 256 : 512;
-    static constexpr int kMinBlocks = kSmall ? (sizeof(T) == 4 ? 3 : 2) : 1;
-};
 // block sizes with a compile-time plan
 template <typename T> inline bool fast_supported(int logb) {
     return sizeof(T) == 4 ? (logb >= 12 && logb <= 15) : (logb >= 12 && logb <= 14);

@@ -19,6 +19,7 @@
 namespace gp {
 static thread_local std::string t_last_error;
 std::atomic<uint64_t> g_launches{0};
+thread_local cudaStream_t tl_stream = nullptr;
 
 int set_error(const char *msg) {
     t_last_error = msg ? msg : "unknown error";
@@ -60,6 +61,12 @@ void free_context(GpuContext *ctx) {
     if (ctx->d_fwd) cudaFree(ctx->d_fwd);
     if (ctx->d_inv) cudaFree(ctx->d_inv);
     if (ctx->d_limb) cudaFree(ctx->d_limb);
+    for (int i = 0; i < 2; i++) {
+        if (ctx->aux[i]) cudaStreamSynchronize(ctx->aux[i]);
+        if (ctx->aux[i]) cudaStreamDestroy(ctx->aux[i]);
+        if (ctx->ev_join[i]) cudaEventDestroy(ctx->ev_join[i]);
+    }
+    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -127,6 +134,11 @@ int gpu_context_create(uint32_t logN, uint32_t L, uint32_t dnum, const uint64_t 
         ctx->sm_count = prop.multiProcessorCount;
         ctx->max_smem_optin = (int)prop.sharedMemPerBlockOptin;
         GP_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking), "cudaStreamCreate");
+        for (int i = 0; i < 2; i++) {
+            GP_CUDA(cudaStreamCreateWithFlags(&ctx->aux[i], cudaStreamNonBlocking), "cudaStreamCreate(aux)");
+            GP_CUDA(cudaEventCreateWithFlags(&ctx->ev_join[i], cudaEventDisableTiming), "cudaEventCreate(aux)");
+        }
+        GP_CUDA(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming), "cudaEventCreate(fork)");
         if (ctx->wide) upload_tables<uint64_t>(ctx);
         else upload_tables<uint32_t>(ctx);
         *out_ctx = ctx;

@@ -14,9 +14,9 @@ int launch_elementwise(GpuContext *ctx, T *out, const T *a, const T *b, size_t w
     const auto *lc = (const gp::LimbConst<T> *)ctx->d_limb;
     const uint32_t logn = (uint32_t)ctx->logN;
     switch (V) {
-        case 4: gp::elementwise_kernel<T, 4, OP><<<grid, threads, 0, ctx->stream>>>(out, a, b, total, limbs, logn, lc); break;
-        case 2: gp::elementwise_kernel<T, 2, OP><<<grid, threads, 0, ctx->stream>>>(out, a, b, total, limbs, logn, lc); break;
-        default: gp::elementwise_kernel<T, 1, OP><<<grid, threads, 0, ctx->stream>>>(out, a, b, total, limbs, logn, lc); break;
+        case 4: gp::elementwise_kernel<T, 4, OP><<<grid, threads, 0, gp::cur(ctx)>>>(out, a, b, total, limbs, logn, lc); break;
+        case 2: gp::elementwise_kernel<T, 2, OP><<<grid, threads, 0, gp::cur(ctx)>>>(out, a, b, total, limbs, logn, lc); break;
+        default: gp::elementwise_kernel<T, 1, OP><<<grid, threads, 0, gp::cur(ctx)>>>(out, a, b, total, limbs, logn, lc); break;
     }
     gp::count_launch();
     GP_CHECK_LAUNCH("elementwise_kernel");
@@ -28,7 +28,7 @@ int launch_matmul_tile(GpuContext *ctx, T *out, const T *A, const T *B, const gp
     const unsigned threads = 128;
     const unsigned per_limb = (unsigned)(((size_t)ctx->N / V + threads - 1) / threads);
     dim3 grid(g.limbs * per_limb, (g.cols + TC - 1) / TC, (g.rows + TR - 1) / TR);
-    gp::matmul_kernel<T, V, TR, TC><<<grid, threads, 0, ctx->stream>>>(out, A, B, g, (const gp::LimbConst<T> *)ctx->d_limb);
+    gp::matmul_kernel<T, V, TR, TC><<<grid, threads, 0, gp::cur(ctx)>>>(out, A, B, g, (const gp::LimbConst<T> *)ctx->d_limb);
     gp::count_launch();
     GP_CHECK_LAUNCH("matmul_kernel");
     return 0;
@@ -44,7 +44,7 @@ template <typename T> int run_matmul(GpuContext *ctx, T *out, const T *A, const 
     if (g.inner == 0) {  // empty sum: the zero matrix
         for (uint32_t r = 0; r < g.rows; r++)
             GP_CUDA(cudaMemsetAsync(out + ((size_t)r * g.out_cols + g.out_col0) * ((size_t)g.limbs << g.logn), 0,
-                                    (size_t)g.cols * ((size_t)g.limbs << g.logn) * sizeof(T), ctx->stream),
+                                    (size_t)g.cols * ((size_t)g.limbs << g.logn) * sizeof(T), gp::cur(ctx)),
                     "cudaMemsetAsync(matmul)");
         return 0;
     }
@@ -121,9 +121,9 @@ extern "C" int gpu_matrix_add_block(GpuMatrix *out, const GpuMatrix *src, size_t
         const auto *lc = (const gp::LimbConst<T> *)ctx->d_limb; const uint32_t limbs = (uint32_t)out->limbs(), logn = (uint32_t)ctx->logN;
         T *d = (T *)out->data; const T *s = (const T *)src->data;
         switch (V) {
-            case 4: gp::add_rect_kernel<T, 4><<<grid, threads, 0, ctx->stream>>>(d, s, g, total, limbs, logn, lc); break;
-            case 2: gp::add_rect_kernel<T, 2><<<grid, threads, 0, ctx->stream>>>(d, s, g, total, limbs, logn, lc); break;
-            default: gp::add_rect_kernel<T, 1><<<grid, threads, 0, ctx->stream>>>(d, s, g, total, limbs, logn, lc); break;
+            case 4: gp::add_rect_kernel<T, 4><<<grid, threads, 0, gp::cur(ctx)>>>(d, s, g, total, limbs, logn, lc); break;
+            case 2: gp::add_rect_kernel<T, 2><<<grid, threads, 0, gp::cur(ctx)>>>(d, s, g, total, limbs, logn, lc); break;
+            default: gp::add_rect_kernel<T, 1><<<grid, threads, 0, gp::cur(ctx)>>>(d, s, g, total, limbs, logn, lc); break;
         } gp::count_launch();
         GP_CHECK_LAUNCH("add_rect_kernel"); return 0;);
 }
@@ -172,9 +172,9 @@ extern "C" int gpu_matrix_equal(const GpuMatrix *lhs, const GpuMatrix *rhs, int 
         const unsigned threads = 256, grid = stride_grid(ctx, total, threads);
         const T *a = (const T *)lhs->data; const T *b = (const T *)rhs->data;
         switch (V) {
-            case 4: gp::equal_kernel<T, 4><<<grid, threads, 0, ctx->stream>>>(a, b, total, (int *)flag.p); break;
-            case 2: gp::equal_kernel<T, 2><<<grid, threads, 0, ctx->stream>>>(a, b, total, (int *)flag.p); break;
-            default: gp::equal_kernel<T, 1><<<grid, threads, 0, ctx->stream>>>(a, b, total, (int *)flag.p); break;
+            case 4: gp::equal_kernel<T, 4><<<grid, threads, 0, gp::cur(ctx)>>>(a, b, total, (int *)flag.p); break;
+            case 2: gp::equal_kernel<T, 2><<<grid, threads, 0, gp::cur(ctx)>>>(a, b, total, (int *)flag.p); break;
+            default: gp::equal_kernel<T, 1><<<grid, threads, 0, gp::cur(ctx)>>>(a, b, total, (int *)flag.p); break;
         } gp::count_launch();
         GP_CHECK_LAUNCH("equal_kernel"); return 0;);
     if (st) return st;

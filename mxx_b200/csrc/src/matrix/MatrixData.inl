@@ -33,9 +33,9 @@ int launch_copy_rect(GpuContext *ctx, T *dst, const T *src, const gp::RectGeom &
     const size_t total = words / V;
     const unsigned threads = 256, grid = stride_grid(ctx, total, threads);
     switch (V) {
-        case 4: gp::copy_rect_kernel<T, 4><<<grid, threads, 0, ctx->stream>>>(dst, src, g, total, poly_words); break;
-        case 2: gp::copy_rect_kernel<T, 2><<<grid, threads, 0, ctx->stream>>>(dst, src, g, total, poly_words); break;
-        default: gp::copy_rect_kernel<T, 1><<<grid, threads, 0, ctx->stream>>>(dst, src, g, total, poly_words); break;
+        case 4: gp::copy_rect_kernel<T, 4><<<grid, threads, 0, gp::cur(ctx)>>>(dst, src, g, total, poly_words); break;
+        case 2: gp::copy_rect_kernel<T, 2><<<grid, threads, 0, gp::cur(ctx)>>>(dst, src, g, total, poly_words); break;
+        default: gp::copy_rect_kernel<T, 1><<<grid, threads, 0, gp::cur(ctx)>>>(dst, src, g, total, poly_words); break;
     }
     gp::count_launch();
     GP_CHECK_LAUNCH("copy_rect_kernel");

@@ -30,7 +30,7 @@ int run_fill_gadget(GpuContext *ctx, GpuMatrix *out, uint32_t base_bits, bool sm
             "cudaMemcpyAsync(gadget table)");
     const size_t words = out->polys() * out->poly_words();
     const unsigned threads = 256, grid = stride_grid(ctx, words, threads);
-    gp::gadget_fill_kernel<T><<<grid, threads, 0, ctx->stream>>>((T *)out->data, (const T *)tab.p, words, (uint32_t)out->rows, ell,
+    gp::gadget_fill_kernel<T><<<grid, threads, 0, gp::cur(ctx)>>>((T *)out->data, (const T *)tab.p, words, (uint32_t)out->rows, ell,
                                                                dpt, limbs, (uint32_t)ctx->logN, small ? 1 : 0);
     gp::count_launch();
     GP_CHECK_LAUNCH("gadget_fill_kernel");
@@ -57,7 +57,7 @@ int launch_fast_decompose(GpuContext *ctx, const T *src, T *out, const gp::Decom
     constexpr size_t smem = gp::fast_smem_bytes<T, LOGB>();
     auto kernel = gp::fast_decompose_kernel<T, LOGB, NOCSUB>;
     if (optin_smem(kernel, smem, ctx->device, done)) return 1;
-    kernel<<<grid, gp::FastCfg<T, LOGB>::kThreads, smem, ctx->stream>>>(src, out, g, (const gp::TwPair<T> *)ctx->d_fwd,
+    kernel<<<grid, gp::FastCfg<T, LOGB>::kThreads, smem, gp::cur(ctx)>>>(src, out, g, (const gp::TwPair<T> *)ctx->d_fwd,
                                                                        (const gp::LimbConst<T> *)ctx->d_limb);
     gp::count_launch();
     GP_CHECK_LAUNCH("fast_decompose_kernel");
@@ -92,12 +92,12 @@ int run_decompose(GpuContext *ctx, const T *src_coeff, T *out, size_t rows, size
     const auto *lc = (const gp::LimbConst<T> *)ctx->d_limb;
     const unsigned grid = (unsigned)(opl << top), threads = gp::NttCfg<T>::kThreads;
     if (to_eval && top == 0) {
-        gp::decompose_kernel<T, true><<<grid, threads, smem, ctx->stream>>>(src_coeff, out, g, (uint32_t)logn, (uint32_t)logb, tw, lc);
+        gp::decompose_kernel<T, true><<<grid, threads, smem, gp::cur(ctx)>>>(src_coeff, out, g, (uint32_t)logn, (uint32_t)logb, tw, lc);
         gp::count_launch();
         GP_CHECK_LAUNCH("decompose_kernel");
         return 0;
     }
-    gp::decompose_kernel<T, false><<<grid, threads, 0, ctx->stream>>>(src_coeff, out, g, (uint32_t)logn, (uint32_t)logb, tw, lc);
+    gp::decompose_kernel<T, false><<<grid, threads, 0, gp::cur(ctx)>>>(src_coeff, out, g, (uint32_t)logn, (uint32_t)logb, tw, lc);
     gp::count_launch();
     GP_CHECK_LAUNCH("decompose_kernel");
     if (to_eval) return run_ntt_fwd<T>(ctx, out, out, rows * g.ell * cols, limbs);
@@ -172,9 +172,9 @@ extern "C" int gpu_matrix_fill_small_decomposed_identity_chunk(GpuMatrix *out, c
         const unsigned threads = 256, grid = stride_grid(ctx, total, threads);
         T *d = (T *)out->data; const T *s = (const T *)scalar_by_digit->data;
         switch (V) {
-            case 4: gp::small_identity_chunk_kernel<T, 4><<<grid, threads, 0, ctx->stream>>>(d, s, size, chunk_idx, digits, total, pw); break;
-            case 2: gp::small_identity_chunk_kernel<T, 2><<<grid, threads, 0, ctx->stream>>>(d, s, size, chunk_idx, digits, total, pw); break;
-            default: gp::small_identity_chunk_kernel<T, 1><<<grid, threads, 0, ctx->stream>>>(d, s, size, chunk_idx, digits, total, pw); break;
+            case 4: gp::small_identity_chunk_kernel<T, 4><<<grid, threads, 0, gp::cur(ctx)>>>(d, s, size, chunk_idx, digits, total, pw); break;
+            case 2: gp::small_identity_chunk_kernel<T, 2><<<grid, threads, 0, gp::cur(ctx)>>>(d, s, size, chunk_idx, digits, total, pw); break;
+            default: gp::small_identity_chunk_kernel<T, 1><<<grid, threads, 0, gp::cur(ctx)>>>(d, s, size, chunk_idx, digits, total, pw); break;
         } gp::count_launch();
         GP_CHECK_LAUNCH("small_identity_chunk_kernel"); return 0;);
 }
@@ -210,21 +210,40 @@ extern "C" int gpu_matrix_mul_decompose(GpuMatrix *out, const GpuMatrix *lhs, co
         if (end && end != env && v) budget = v;
     }
     const uint32_t limbs = (uint32_t)out->limbs();
+    // Column chunks are independent.  Chunk k runs on auxiliary stream k % 2 with its own
+    // digit buffer, so the partial last wave of one chunk's digit-NTT kernel is filled by the next
+    // chunk's CTAs and the HBM/L2-bound product kernel overlaps the issue-bound NTT kernel.
     return GP_DISPATCH_WIDTH(
         ctx, const size_t poly_bytes = out->poly_words() * sizeof(T);
-        size_t width = std::max<size_t>(1, budget / std::max<size_t>(1, m * poly_bytes)); width = std::min(width, c);
-        const T *coeff = (const T *)rhs->data; Scratch tmp; Scratch digits;
+        size_t width = std::max<size_t>(1, (budget / 2) / std::max<size_t>(1, m * poly_bytes)); width = std::min(width, c);
+        const size_t chunks = (c + width - 1) / width; const int lanes = chunks > 1 ? 2 : 1;
+        const T *coeff = (const T *)rhs->data; Scratch tmp; Scratch digits[2];
         if (rhs->format == GPU_POLY_FORMAT_EVAL) {
             if (tmp.alloc(rhs->bytes(), ctx->stream)) return 1;
             if (run_ntt_inv<T>(ctx, (const T *)rhs->data, (T *)tmp.p, rhs->polys(), limbs)) return 1;
             coeff = (const T *)tmp.p;
-        } if (digits.alloc(m * width * poly_bytes, ctx->stream)) return 1;
-        for (size_t c0 = 0; c0 < c; c0 += width) {
-            const size_t w = std::min(width, c - c0);
-            if (run_decompose<T>(ctx, coeff, (T *)digits.p, d, c, c0, w, limbs, base_bits, small != 0, true)) return 1;
+        }
+        for (int i = 0; i < lanes; i++) if (digits[i].alloc(m * width * poly_bytes, ctx->stream)) return 1;
+        if (lanes > 1) {
+            GP_CUDA(cudaEventRecord(ctx->ev_fork, ctx->stream), "cudaEventRecord(fork)");
+            for (int i = 0; i < lanes; i++) GP_CUDA(cudaStreamWaitEvent(ctx->aux[i], ctx->ev_fork, 0), "cudaStreamWaitEvent(fork)");
+        }
+        int st = 0;
+        for (size_t k = 0; k < chunks && !st; k++) {
+            const size_t c0 = k * width, w = std::min(width, c - c0);
+            gp::StreamScope scope(lanes > 1 ? ctx->aux[k & 1] : ctx->stream);
+            T *dg = (T *)digits[lanes > 1 ? (k & 1) : 0].p;
+            st = run_decompose<T>(ctx, coeff, dg, d, c, c0, w, limbs, base_bits, small != 0, true);
+            if (st) break;
             gp::MatmulGeom g{};
             g.rows = (uint32_t)lhs->rows; g.inner = (uint32_t)m; g.cols = (uint32_t)w; g.b_cols = (uint32_t)w; g.b_col0 = 0;
             g.out_cols = (uint32_t)c; g.out_col0 = (uint32_t)c0; g.limbs = limbs;
-            if (run_matmul<T>(ctx, (T *)out->data, (const T *)lhs->data, (const T *)digits.p, g)) return 1;
-        } return 0;);
+            st = run_matmul<T>(ctx, (T *)out->data, (const T *)lhs->data, dg, g);
+        }
+        if (lanes > 1)  // join even after an error so the scratch buffers are not freed under running kernels
+            for (int i = 0; i < lanes; i++) {
+                cudaEventRecord(ctx->ev_join[i], ctx->aux[i]);
+                cudaStreamWaitEvent(ctx->stream, ctx->ev_join[i], 0);
+            }
+        return st;);
 }

@@ -34,7 +34,7 @@ int launch_fast_fwd(GpuContext *ctx, const T *src, T *dst, unsigned grid, uint32
     constexpr size_t smem = gp::fast_smem_bytes<T, LOGB>();
     auto kernel = gp::fast_ntt_fwd_kernel<T, LOGB, NOCSUB>;
     if (optin_smem(kernel, smem, ctx->device, done)) return 1;
-    kernel<<<grid, gp::FastCfg<T, LOGB>::kThreads, smem, ctx->stream>>>(src, dst, limbs, (uint32_t)ctx->logN,
+    kernel<<<grid, gp::FastCfg<T, LOGB>::kThreads, smem, gp::cur(ctx)>>>(src, dst, limbs, (uint32_t)ctx->logN,
                                                                        (const gp::TwPair<T> *)ctx->d_fwd,
                                                                        (const gp::LimbConst<T> *)ctx->d_limb);
     gp::count_launch();
@@ -47,7 +47,7 @@ int launch_fast_inv(GpuContext *ctx, const T *src, T *dst, unsigned grid, uint32
     constexpr size_t smem = gp::fast_smem_bytes<T, LOGB>();
     auto kernel = gp::fast_ntt_inv_kernel<T, LOGB>;
     if (optin_smem(kernel, smem, ctx->device, done)) return 1;
-    kernel<<<grid, gp::FastCfg<T, LOGB>::kThreads, smem, ctx->stream>>>(src, dst, limbs, (uint32_t)ctx->logN,
+    kernel<<<grid, gp::FastCfg<T, LOGB>::kThreads, smem, gp::cur(ctx)>>>(src, dst, limbs, (uint32_t)ctx->logN,
                                                                        (const gp::TwPair<T> *)ctx->d_inv,
                                                                        (const gp::LimbConst<T> *)ctx->d_limb);
     gp::count_launch();
@@ -92,7 +92,7 @@ template <typename T, int LOGR>
 int launch_fwd_global(GpuContext *ctx, T *data, size_t pl, uint32_t limbs, uint32_t lspan) {
     const size_t total = pl << (ctx->logN - LOGR);
     const unsigned threads = 256, grid = (unsigned)((total + threads - 1) / threads);
-    gp::ntt_fwd_global_pass<T, LOGR><<<grid, threads, 0, ctx->stream>>>(data, total, limbs, (uint32_t)ctx->logN, lspan,
+    gp::ntt_fwd_global_pass<T, LOGR><<<grid, threads, 0, gp::cur(ctx)>>>(data, total, limbs, (uint32_t)ctx->logN, lspan,
                                                                          (const gp::TwPair<T> *)ctx->d_fwd,
                                                                          (const gp::LimbConst<T> *)ctx->d_limb);
     gp::count_launch();
@@ -106,9 +106,9 @@ int launch_inv_global(GpuContext *ctx, T *data, size_t pl, uint32_t limbs, uint3
     const auto *tw = (const gp::TwPair<T> *)ctx->d_inv;
     const auto *lc = (const gp::LimbConst<T> *)ctx->d_limb;
     if (final_pass)
-        gp::ntt_inv_global_pass<T, LOGR, true><<<grid, threads, 0, ctx->stream>>>(data, total, limbs, (uint32_t)ctx->logN, lt0, tw, lc);
+        gp::ntt_inv_global_pass<T, LOGR, true><<<grid, threads, 0, gp::cur(ctx)>>>(data, total, limbs, (uint32_t)ctx->logN, lt0, tw, lc);
     else
-        gp::ntt_inv_global_pass<T, LOGR, false><<<grid, threads, 0, ctx->stream>>>(data, total, limbs, (uint32_t)ctx->logN, lt0, tw, lc);
+        gp::ntt_inv_global_pass<T, LOGR, false><<<grid, threads, 0, gp::cur(ctx)>>>(data, total, limbs, (uint32_t)ctx->logN, lt0, tw, lc);
     gp::count_launch();
     GP_CHECK_LAUNCH("ntt_inv_global_pass");
     return 0;
@@ -142,7 +142,7 @@ template <typename T> int run_ntt_fwd(GpuContext *ctx, const T *src, T *dst, siz
     if (!fast && ensure_ntt_smem<T>(ctx, smem)) return 1;
     if (top > 0) {
         if (src != dst)
-            GP_CUDA(cudaMemcpyAsync(dst, src, (pl << logn) * sizeof(T), cudaMemcpyDeviceToDevice, ctx->stream), "cudaMemcpyAsync(ntt)");
+            GP_CUDA(cudaMemcpyAsync(dst, src, (pl << logn) * sizeof(T), cudaMemcpyDeviceToDevice, gp::cur(ctx)), "cudaMemcpyAsync(ntt)");
         src = dst;
         int passes[8], np = 0;
         split_top(top, passes, &np);
@@ -154,7 +154,7 @@ template <typename T> int run_ntt_fwd(GpuContext *ctx, const T *src, T *dst, siz
     }
     const unsigned grid = (unsigned)(pl << top);
     if (fast) return dispatch_fast_fwd<T>(ctx, src, dst, grid, limbs, logb);
-    gp::ntt_fwd_kernel<T><<<grid, gp::NttCfg<T>::kThreads, smem, ctx->stream>>>(
+    gp::ntt_fwd_kernel<T><<<grid, gp::NttCfg<T>::kThreads, smem, gp::cur(ctx)>>>(
         src, dst, limbs, (uint32_t)logn, (uint32_t)logb, (const gp::TwPair<T> *)ctx->d_fwd, (const gp::LimbConst<T> *)ctx->d_limb);
     gp::count_launch();
     GP_CHECK_LAUNCH("ntt_fwd_kernel");
@@ -172,7 +172,7 @@ template <typename T> int run_ntt_inv(GpuContext *ctx, const T *src, T *dst, siz
         if (dispatch_fast_inv<T>(ctx, src, dst, grid, limbs, logb)) return 1;
     } else {
         if (ensure_ntt_smem<T>(ctx, smem)) return 1;
-        gp::ntt_inv_kernel<T><<<grid, gp::NttCfg<T>::kThreads, smem, ctx->stream>>>(
+        gp::ntt_inv_kernel<T><<<grid, gp::NttCfg<T>::kThreads, smem, gp::cur(ctx)>>>(
             src, dst, limbs, (uint32_t)logn, (uint32_t)logb, (const gp::TwPair<T> *)ctx->d_inv, (const gp::LimbConst<T> *)ctx->d_limb);
         gp::count_launch();
         GP_CHECK_LAUNCH("ntt_inv_kernel");

@@ -27,9 +27,9 @@ template <typename T>
 int launch_pack(GpuContext *ctx, T *dst, const uint64_t *src, size_t words, bool bitrev) {
     const unsigned threads = 256, grid = stride_grid(ctx, words, threads);
     if (bitrev)
-        gp::pack_kernel<T, true><<<grid, threads, 0, ctx->stream>>>(dst, src, words, (uint32_t)ctx->logN);
+        gp::pack_kernel<T, true><<<grid, threads, 0, gp::cur(ctx)>>>(dst, src, words, (uint32_t)ctx->logN);
     else
-        gp::pack_kernel<T, false><<<grid, threads, 0, ctx->stream>>>(dst, src, words, (uint32_t)ctx->logN);
+        gp::pack_kernel<T, false><<<grid, threads, 0, gp::cur(ctx)>>>(dst, src, words, (uint32_t)ctx->logN);
     gp::count_launch();
     GP_CHECK_LAUNCH("pack_kernel");
     return 0;
@@ -38,9 +38,9 @@ template <typename T>
 int launch_unpack(GpuContext *ctx, uint64_t *dst, const T *src, size_t words, bool bitrev) {
     const unsigned threads = 256, grid = stride_grid(ctx, words, threads);
     if (bitrev)
-        gp::unpack_kernel<T, true><<<grid, threads, 0, ctx->stream>>>(dst, src, words, (uint32_t)ctx->logN);
+        gp::unpack_kernel<T, true><<<grid, threads, 0, gp::cur(ctx)>>>(dst, src, words, (uint32_t)ctx->logN);
     else
-        gp::unpack_kernel<T, false><<<grid, threads, 0, ctx->stream>>>(dst, src, words, (uint32_t)ctx->logN);
+        gp::unpack_kernel<T, false><<<grid, threads, 0, gp::cur(ctx)>>>(dst, src, words, (uint32_t)ctx->logN);
     gp::count_launch();
     GP_CHECK_LAUNCH("unpack_kernel");
     return 0;
@@ -133,10 +133,10 @@ extern "C" int gpu_matrix_store_const_coeff_batch(const GpuMatrix *mat, uint64_t
     if (stage.alloc(count * sizeof(uint64_t), ctx->stream)) return 1;
     const unsigned threads = 256, grid = (unsigned)((count + threads - 1) / threads);
     if (ctx->wide)
-        gp::const_coeff_kernel<uint64_t><<<grid, threads, 0, ctx->stream>>>((uint64_t *)stage.p, (const uint64_t *)mat->data, count,
+        gp::const_coeff_kernel<uint64_t><<<grid, threads, 0, gp::cur(ctx)>>>((uint64_t *)stage.p, (const uint64_t *)mat->data, count,
                                                                             (uint32_t)ctx->logN);
     else
-        gp::const_coeff_kernel<uint32_t><<<grid, threads, 0, ctx->stream>>>((uint64_t *)stage.p, (const uint32_t *)mat->data, count,
+        gp::const_coeff_kernel<uint32_t><<<grid, threads, 0, gp::cur(ctx)>>>((uint64_t *)stage.p, (const uint32_t *)mat->data, count,
                                                                             (uint32_t)ctx->logN);
     gp::count_launch();
     GP_CHECK_LAUNCH("const_coeff_kernel");

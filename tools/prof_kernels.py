@@ -7,13 +7,14 @@ import sys
 
 import numpy as np
 
+REPS = int(os.environ.get("PROF_REPS", "3"))
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from bench import uniform_host  # noqa: E402
 from mxx_b200 import GpuDCRTPolyMatrix, GpuDCRTPolyParams, ffi, standard_moduli  # noqa: E402
 
 
-def ntt(n, depth, bits, polys, reps=2):
+def ntt(n, depth, bits, polys, reps=REPS):
     moduli = standard_moduli(n, depth, bits)
     params = GpuDCRTPolyParams(n, moduli, 14)
     host = np.empty((1, polys, depth, n), dtype=np.uint64)
@@ -34,7 +35,7 @@ def ntt(n, depth, bits, polys, reps=2):
     assert np.array_equal(m.to_rns(), host)
 
 
-def md(reps=2):
+def md(reps=REPS):
     n, depth, bits, bb = 1 << 14, 15, 24, 12
     moduli = standard_moduli(n, depth, bits)
     params = GpuDCRTPolyParams(n, moduli, bb)
@@ -53,7 +54,7 @@ def md(reps=2):
     return out
 
 
-def mul(reps=2):
+def mul(reps=REPS):
     n, depth, bits = 1 << 14, 15, 24
     moduli = standard_moduli(n, depth, bits)
     params = GpuDCRTPolyParams(n, moduli, 12)
