@@ -19,6 +19,32 @@ template <typename T, int V> GP_HD void stv(T *p, const Vec<T, V> &x) {
     *reinterpret_cast<Vec<T, V> *>(p) = x;
 }
 
+// streaming variants (read-once / write-once data: evict-first, so that the operand every CTA re-reads
+// — the left matrix of a product — stays resident in L2 while the right matrix streams through)
+template <typename T, int V> GP_HD Vec<T, V> ldv_stream(const T *p) {
+#ifdef __CUDA_ARCH__
+    if constexpr (sizeof(T) * V == 16) {
+        const uint4 r = __ldcs(reinterpret_cast<const uint4 *>(p));
+        Vec<T, V> out;
+        *reinterpret_cast<uint4 *>(&out) = r;
+        return out;
+    } else
+#endif
+    {
+        return ldv<T, V>(p);
+    }
+}
+template <typename T, int V> GP_HD void stv_stream(T *p, const Vec<T, V> &x) {
+#ifdef __CUDA_ARCH__
+    if constexpr (sizeof(T) * V == 16) {
+        __stcs(reinterpret_cast<uint4 *>(p), *reinterpret_cast<const uint4 *>(&x));
+    } else
+#endif
+    {
+        stv<T, V>(p, x);
+    }
+}
+
 enum class EwOp { Add, Sub, MulScalar };
 
 // out[p] = a[p] (+|-) b[p], or a[p] * s (s one poly).  total = words / V.
@@ -159,7 +185,7 @@ struct MatmulGeom {
     uint32_t out_cols, out_col0;  // the product lands in columns [out_col0, out_col0 + cols) of out
     uint32_t limbs, logn, fold;
 };
-template <typename T, int V, int TR, int TC>
+template <typename T, int V, int TR, int TC, int UNROLL = 2>
 GP_HD void matmul_thread(uint32_t bx, uint32_t by, uint32_t bz, uint32_t tid, uint32_t ntid, T *__restrict__ out,
                          const T *__restrict__ A, const T *__restrict__ B, const MatmulGeom &g,
                          const LimbConst<T> *__restrict__ lc) {
@@ -190,13 +216,14 @@ GP_HD void matmul_thread(uint32_t bx, uint32_t by, uint32_t bz, uint32_t tid, ui
     const size_t bstep = (size_t)g.b_cols * poly_words;
 
     uint32_t since = 0;
-#pragma unroll 2
+    constexpr int kUnroll = UNROLL;
+#pragma unroll kUnroll
     for (uint32_t k = 0; k < inner; k++) {
         Vec<T, V> a[TR], b[TC];
 #pragma unroll
         for (int i = 0; i < TR; i++) a[i] = ldv<T, V>(A + arow[i] + (size_t)k * poly_words);
 #pragma unroll
-        for (int j = 0; j < TC; j++) b[j] = ldv<T, V>(B + bcol[j] + (size_t)k * bstep);
+        for (int j = 0; j < TC; j++) b[j] = ldv_stream<T, V>(B + bcol[j] + (size_t)k * bstep);
 #pragma unroll
         for (int i = 0; i < TR; i++)
 #pragma unroll
@@ -221,15 +248,18 @@ GP_HD void matmul_thread(uint32_t bx, uint32_t by, uint32_t bz, uint32_t tid, ui
                 Vec<T, V> o;
 #pragma unroll
                 for (int v = 0; v < V; v++) o.v[v] = acc[i][j][v].result(c);
-                stv<T, V>(out + ((size_t)(r0 + i) * g.out_cols + g.out_col0 + c0 + j) * poly_words + in_poly, o);
+                stv_stream<T, V>(out + ((size_t)(r0 + i) * g.out_cols + g.out_col0 + c0 + j) * poly_words + in_poly, o);
             }
         }
 }
-template <typename T, int V, int TR, int TC>
-__global__ void __launch_bounds__(128)
+// UNROLL (inner-dimension unroll) and NT (CTA size) are tuned per tile shape on the C1-R product
+// (tools/matmul_lab.cu): <1,6> unroll 2 / 64 threads and <1,1> unroll 6 / 128 threads stream the right
+// operand at the measured HBM copy bandwidth; see DESIGN.md 4.
+template <typename T, int V, int TR, int TC, int UNROLL = 2, int NT = 128>
+__global__ void __launch_bounds__(NT)
 matmul_kernel(T *__restrict__ out, const T *__restrict__ A, const T *__restrict__ B, MatmulGeom g,
               const LimbConst<T> *__restrict__ lc) {
-    matmul_thread<T, V, TR, TC>(blockIdx.x, blockIdx.y, blockIdx.z, threadIdx.x, blockDim.x, out, A, B, g, lc);
+    matmul_thread<T, V, TR, TC, UNROLL>(blockIdx.x, blockIdx.y, blockIdx.z, threadIdx.x, blockDim.x, out, A, B, g, lc);
 }
 
 }  // namespace gp

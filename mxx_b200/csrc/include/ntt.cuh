@@ -50,11 +50,16 @@ template <typename T> struct DigitSrc {
     uint32_t shift;
     T mask;
     T q;
+    T one_s;  // floor(2^wordbits / q)
+    // digit in [0, 2q): a digit can only exceed the target modulus when its mask does (a CTA-uniform
+    // test), and then one Shoup-multiply-by-one brings it below 2q — the transforms accept that range
     GP_HD T xform(T raw) const {
         T d = (raw >> shift) & mask;
-        return d >= q ? d % q : d;
+        if (mask >= q) d = d - mulhi(d, one_s) * q;
+        return d;
     }
     GP_HD T operator()(uint32_t i) const { return xform(p[i]); }
+    GP_HD T canonical(uint32_t i) const { return csub<T>(xform(p[i]), q); }  // [0, q): coefficient-form output
 };
 
 // ---- register butterfly networks ------------------------------------------------
@@ -327,12 +332,12 @@ GP_HD void decompose_cta(uint32_t bid, T *sm, const T *__restrict__ src, T *__re
     }
     const T *sp = src + (((row * g.src_cols + g.src_col0 + col) * g.limbs + t) << logn) + ((size_t)sb << logb);
     T *dp = out + (pl << logn) + ((size_t)sb << logb);
-    DigitSrc<T> dsrc{sp, shift >= sizeof(T) * 8 ? 0u : shift, shift >= sizeof(T) * 8 ? (T)0 : mask, c.q};
+    DigitSrc<T> dsrc{sp, shift >= sizeof(T) * 8 ? 0u : shift, shift >= sizeof(T) * 8 ? (T)0 : mask, c.q, c.one_s};
     if (TO_EVAL) {
         fwd_block<T>(dsrc, dp, sm, logn, logb, sb, tw_all + ((size_t)limb << logn), c);
     } else {
         const uint32_t B = 1u << logb;
-        for (uint32_t i = GP_TID; i < B; i += GP_NT) dp[i] = dsrc(i);
+        for (uint32_t i = GP_TID; i < B; i += GP_NT) dp[i] = dsrc.canonical(i);
     }
 }
 template <typename T, bool TO_EVAL>

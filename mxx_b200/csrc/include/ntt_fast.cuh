@@ -595,7 +595,7 @@ GP_HD void fast_decompose_cta(uint32_t bid, void *smem, const T *__restrict__ sr
         mask = db >= sizeof(T) * 8 ? ~(T)0 : (T)(((T)1 << db) - 1);
     }
     const T *sp = src + (((row * g.src_cols + g.src_col0 + col) * g.limbs + t) << LOGB);
-    DigitSrc<T> dsrc{sp, shift >= sizeof(T) * 8 ? 0u : shift, shift >= sizeof(T) * 8 ? (T)0 : mask, c.q};
+    DigitSrc<T> dsrc{sp, shift >= sizeof(T) * 8 ? 0u : shift, shift >= sizeof(T) * 8 ? (T)0 : mask, c.q, c.one_s};
     fast_fwd_block<T, LOGB, NOCSUB>(dsrc, out + (pl << LOGB), smem, LOGB, 0, tw_all + ((size_t)limb << LOGB), c);
 }
 template <typename T, int LOGB, bool NOCSUB>

@@ -23,12 +23,12 @@ int launch_elementwise(GpuContext *ctx, T *out, const T *a, const T *b, size_t w
     return 0;
 }
 
-template <typename T, int V, int TR, int TC>
+template <typename T, int V, int TR, int TC, int UNROLL = 2, int NT = 128>
 int launch_matmul_tile(GpuContext *ctx, T *out, const T *A, const T *B, const gp::MatmulGeom &g) {
-    const unsigned threads = 128;
+    const unsigned threads = NT;
     const unsigned per_limb = (unsigned)(((size_t)ctx->N / V + threads - 1) / threads);
     dim3 grid(g.limbs * per_limb, (g.cols + TC - 1) / TC, (g.rows + TR - 1) / TR);
-    gp::matmul_kernel<T, V, TR, TC><<<grid, threads, 0, gp::cur(ctx)>>>(out, A, B, g, (const gp::LimbConst<T> *)ctx->d_limb);
+    gp::matmul_kernel<T, V, TR, TC, UNROLL, NT><<<grid, threads, 0, gp::cur(ctx)>>>(out, A, B, g, (const gp::LimbConst<T> *)ctx->d_limb);
     gp::count_launch();
     GP_CHECK_LAUNCH("matmul_kernel");
     return 0;
@@ -53,7 +53,10 @@ template <typename T> int run_matmul(GpuContext *ctx, T *out, const T *A, const 
     // BGG / bench_matrix_mul shape) streams B once and re-reads A from L2.
     if (g.rows >= 4) return launch_matmul_tile<T, VMAX / 2, 4, 4>(ctx, out, A, B, g);
     if (g.rows >= 2) return launch_matmul_tile<T, VMAX, 2, 4>(ctx, out, A, B, g);
-    return launch_matmul_tile<T, VMAX, 1, 4>(ctx, out, A, B, g);
+    // one output row: the product is a stream over B.  Tile shapes measured on C1-R (tools/matmul_lab.cu):
+    // six columns per thread when the width allows, else one column with a deep unroll.
+    if (g.cols % 6 == 0) return launch_matmul_tile<T, VMAX, 1, 6, 2, 64>(ctx, out, A, B, g);
+    return launch_matmul_tile<T, VMAX, 1, 1, 6, 128>(ctx, out, A, B, g);
 }
 
 int binary_check(const char *name, GpuMatrix *out, const GpuMatrix *lhs, const GpuMatrix *rhs) {

@@ -184,9 +184,8 @@ extern "C" int gpu_matrix_fill_small_decomposed_identity_chunk(GpuMatrix *out, c
 // GpuDCRTPolyMatrix::mul_decompose (src/matrix/gpu_dcrt_poly.rs:1414-1493; ~5 matrix
 // creations and log2(n)+5 launches per column there).  Here: one INTT of `other`, then per
 // column chunk one fused digit+NTT kernel and one product kernel writing straight into the
-// output columns.  The chunk width keeps the digit block inside the 126 MB L2 so the
-// digits are produced and consumed on chip (MXX_MUL_DECOMPOSE_L2_BYTES overrides the
-// budget; the reference's knob is MXX_MUL_DECOMPOSE_COLUMN_CHUNK_WIDTH, src/env.rs:148).
+// output columns (MXX_MUL_DECOMPOSE_SCRATCH_BYTES bounds the digit scratch; the reference's
+// knob is MXX_MUL_DECOMPOSE_COLUMN_CHUNK_WIDTH, src/env.rs:148).
 extern "C" int gpu_matrix_mul_decompose(GpuMatrix *out, const GpuMatrix *lhs, const GpuMatrix *rhs, uint32_t base_bits, int small) {
     if (binary_check("gpu_matrix_mul_decompose", out, lhs, rhs)) return 1;
     if (base_bits == 0 || base_bits >= 63) return gp::set_error("invalid base_bits in gpu_matrix_mul_decompose");
@@ -203,8 +202,10 @@ extern "C" int gpu_matrix_mul_decompose(GpuMatrix *out, const GpuMatrix *lhs, co
     out->format = GPU_POLY_FORMAT_EVAL;
     if (out->polys() == 0) return 0;
     if (bind_device(ctx)) return 1;
-    size_t budget = 48ull << 20;
-    if (const char *env = getenv("MXX_MUL_DECOMPOSE_L2_BYTES")) {
+    // digit polynomials in flight: two lanes of at most this many bytes each (they stream through L2/HBM while
+    // the issue-bound digit-NTT kernel runs, so the traffic is hidden; the cap only bounds scratch memory)
+    size_t budget = 2ull << 30;
+    if (const char *env = getenv("MXX_MUL_DECOMPOSE_SCRATCH_BYTES")) {
         char *end = nullptr;
         unsigned long long v = strtoull(env, &end, 10);
         if (end && end != env && v) budget = v;
@@ -215,7 +216,11 @@ extern "C" int gpu_matrix_mul_decompose(GpuMatrix *out, const GpuMatrix *lhs, co
     // chunk's CTAs and the HBM/L2-bound product kernel overlaps the issue-bound NTT kernel.
     return GP_DISPATCH_WIDTH(
         ctx, const size_t poly_bytes = out->poly_words() * sizeof(T);
-        size_t width = std::max<size_t>(1, (budget / 2) / std::max<size_t>(1, m * poly_bytes)); width = std::min(width, c);
+        // Wide chunks: a digit-NTT launch of w columns has w*m*limbs CTAs, and only a launch of many waves keeps
+        // the last, partial wave cheap (C3-a: 450 CTAs per column on 444 resident slots).  Two chunks run
+        // concurrently on the two auxiliary streams, so one chunk's product overlaps the other's NTTs.
+        size_t width = std::max<size_t>(1, (budget / 2) / std::max<size_t>(1, m * poly_bytes));
+        width = std::min(width, c >= 2 ? (c + 1) / 2 : c);
         const size_t chunks = (c + width - 1) / width; const int lanes = chunks > 1 ? 2 : 1;
         const T *coeff = (const T *)rhs->data; Scratch tmp; Scratch digits[2];
         if (rhs->format == GPU_POLY_FORMAT_EVAL) {

@@ -183,7 +183,7 @@ def test_mul_decompose_chunked_workspace(mx, monkeypatch):
     params, plan = setup(mx, 1024, 3, 24, 12)
     ell = plan.ell(12)
     S, other = plan.uniform(2, ell, seed=12), plan.uniform(1, 5, seed=13)
-    monkeypatch.setenv("MXX_MUL_DECOMPOSE_L2_BYTES", str(2 * ell * 3 * 1024 * 4))  # two columns per chunk
+    monkeypatch.setenv("MXX_MUL_DECOMPOSE_SCRATCH_BYTES", str(2 * ell * 3 * 1024 * 4))  # one column per chunk: five chunks over two lanes
     got = G(mx, params, S).mul_decompose(G(mx, params, other), fused=True)
     assert np.array_equal(got.to_rns(), plan.mul_decompose(S, other, 12))
 
