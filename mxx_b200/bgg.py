@@ -1,0 +1,101 @@
+"""BGG+ public keys / encodings over the DCRT matrix path — the caller of the hot path for config C4
+(SURVEY.md 8f-2).  Host mirror of src/bgg/public_key.rs and src/bgg/encoding.rs: same operator names,
+same arithmetic, all of it through the gpu_* C ABI (nothing here touches residues).
+
+    BggPublicKey * BggPublicKey   = A_x.mul_decompose(A_y)                              (public_key.rs:91-105)
+    BggEncoding  * BggEncoding    = (c_x.mul_decompose(A_y) + c_y * x,  A_x.mul_decompose(A_y),  x*y)
+                                                                                        (encoding.rs:125-144)
+
+The reference computes G^-1(A_y) twice per encoding product (encoding.rs:131 and :140).  `fused=True`
+stacks [c_x ; A_x] and issues ONE mul_decompose, so the digit NTTs — the dominant cost — are done once.
+
+`ShardedBggEvaluator` runs a chain of products with the columns of every right operand sharded over the
+ranks (mxx_b200/dist.py): each rank computes its columns of the new vector and public key, and one
+all-gather per gate assembles them, because the next gate needs them whole as its LEFT operand.
+"""
+from __future__ import annotations
+
+from .matrix import GpuDCRTPolyMatrix
+
+
+class BggPublicKey:
+    def __init__(self, matrix: GpuDCRTPolyMatrix, reveal_plaintext: bool = True):
+        self.matrix = matrix
+        self.reveal_plaintext = bool(reveal_plaintext)
+
+    def __add__(self, other):  # public_key.rs:44-61
+        return BggPublicKey(self.matrix + other.matrix, self.reveal_plaintext and other.reveal_plaintext)
+
+    def __sub__(self, other):  # public_key.rs:63-82
+        return BggPublicKey(self.matrix - other.matrix, self.reveal_plaintext and other.reveal_plaintext)
+
+    def __mul__(self, other):  # public_key.rs:91-105
+        return BggPublicKey(self.matrix.mul_decompose(other.matrix), self.reveal_plaintext and other.reveal_plaintext)
+
+    def __eq__(self, other):
+        return self.matrix == other.matrix and self.reveal_plaintext == other.reveal_plaintext
+
+
+class BggEncoding:
+    """vector: 1 x m (m = d * log_base_q), pubkey: d x m, plaintext: a 1x1 matrix (EVAL) or None"""
+
+    def __init__(self, vector: GpuDCRTPolyMatrix, pubkey: BggPublicKey, plaintext: GpuDCRTPolyMatrix | None):
+        self.vector, self.pubkey, self.plaintext = vector, pubkey, plaintext
+
+    def __add__(self, other):  # encoding.rs:57-84
+        pt = self.plaintext + other.plaintext if (self.plaintext is not None and other.plaintext is not None) else None
+        return BggEncoding(self.vector + other.vector, self.pubkey + other.pubkey, pt)
+
+    def __sub__(self, other):  # encoding.rs:86-113
+        pt = self.plaintext - other.plaintext if (self.plaintext is not None and other.plaintext is not None) else None
+        return BggEncoding(self.vector - other.vector, self.pubkey - other.pubkey, pt)
+
+    def mul(self, other, fused: bool = True):  # encoding.rs:125-144
+        if self.plaintext is None:
+            raise ValueError("Unknown plaintext for the left-hand input of multiplication")
+        a_y = other.pubkey.matrix
+        if fused:
+            stacked = self.vector.concat_rows([self.pubkey.matrix])          # [c_x ; A_x], (1 + d) x m
+            prod = stacked.mul_decompose(a_y)                               # one G^-1(A_y)
+            first = prod.slice_rows(0, self.vector.nrow)
+            new_pk = prod.slice_rows(self.vector.nrow, prod.nrow)
+        else:
+            first = self.vector.mul_decompose(a_y)
+            new_pk = self.pubkey.matrix.mul_decompose(a_y)
+        new_vector = first + other.vector.mul_scalar(self.plaintext)
+        pt = self.plaintext * other.plaintext if other.plaintext is not None else None
+        reveal = self.pubkey.reveal_plaintext and other.pubkey.reveal_plaintext
+        return BggEncoding(new_vector, BggPublicKey(new_pk, reveal), pt)
+
+    __mul__ = mul
+
+
+def encode(secret: GpuDCRTPolyMatrix, pubkey: BggPublicKey, plaintext: GpuDCRTPolyMatrix, gadget: GpuDCRTPolyMatrix,
+           error: GpuDCRTPolyMatrix | None = None) -> BggEncoding:
+    """c = s*A - x*(s*G) (+ e): the encoding relation the reference's tests check (src/bgg/mod.rs:98-111)."""
+    vec = secret * pubkey.matrix - (secret * gadget).mul_scalar(plaintext)
+    if error is not None:
+        vec = vec + error
+    return BggEncoding(vec, pubkey, plaintext)
+
+
+class ShardedBggEvaluator:
+    """Chain of encoding products with right operands sharded by columns over the ranks."""
+
+    def __init__(self, ops):
+        self.ops = ops  # mxx_b200.dist.ColumnShardedOps
+
+    def mul_gate(self, left: BggEncoding, right_vec_local: GpuDCRTPolyMatrix, right_pk_local: GpuDCRTPolyMatrix,
+                 right_plaintext: GpuDCRTPolyMatrix | None, ncol: int) -> BggEncoding:
+        """left: whole encoding (replicated); right_*_local: this rank's columns of c_y and A_y.
+        Returns the whole product encoding on every rank (one all-gather of the stacked (1+d) x m block)."""
+        if left.plaintext is None:
+            raise ValueError("Unknown plaintext for the left-hand input of multiplication")
+        stacked = left.vector.concat_rows([left.pubkey.matrix])
+        prod_local = self.ops.mul_decompose(stacked, right_pk_local)                       # no collective
+        vec_rows = left.vector.nrow
+        first = prod_local.slice_rows(0, vec_rows) + right_vec_local.mul_scalar(left.plaintext)
+        local = first.concat_rows([prod_local.slice_rows(vec_rows, prod_local.nrow)])
+        full = self.ops.all_gather_columns(local, ncol)                                    # the exchange step
+        pt = left.plaintext * right_plaintext if right_plaintext is not None else None
+        return BggEncoding(full.slice_rows(0, vec_rows), BggPublicKey(full.slice_rows(vec_rows, full.nrow)), pt)

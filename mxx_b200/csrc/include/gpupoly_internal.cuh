@@ -69,6 +69,7 @@ struct GpuContext {
     void *d_limb = nullptr;  // [L] LimbConst
     bool nocsub = false;             // forward NTT without conditional subtractions (36*qmax fits the word)
     bool force_generic_ntt = false;  // MXX_NTT_GENERIC=1: use only the runtime-planned kernels of ntt.cuh
+    int ntt_block_override = 0;      // MXX_NTT_BLOCK_LOG
     bool smem_configured = false;  // >48 KB dynamic shared memory opted in for the NTT kernels
     uint32_t mac_fold = 1;   // products that fit one lazy accumulator between folds
     size_t word_bytes() const { return wide ? 8 : 4; }

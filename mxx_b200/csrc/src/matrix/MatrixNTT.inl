@@ -10,11 +10,14 @@ namespace {
 // ring, else the generic kernel of ntt.cuh
 template <typename T> inline int ntt_block_log(const GpuContext *ctx) {
     const int fb = gp::fast_block_log<T>(ctx->logN);
+    if (!ctx->force_generic_ntt && ctx->ntt_block_override >= 12 && ctx->ntt_block_override < ctx->logN &&
+        gp::fast_supported<T>(ctx->ntt_block_override))
+        return ctx->ntt_block_override;  // MXX_NTT_BLOCK_LOG: tuning knob for rings above one CTA's shared memory
     if (!ctx->force_generic_ntt && gp::fast_supported<T>(fb)) return fb;
     return gp::ntt_block_log<T>(ctx->logN);
 }
 template <typename T> inline bool use_fast(const GpuContext *ctx, int logb) {
-    return !ctx->force_generic_ntt && gp::fast_supported<T>(logb) && logb == gp::fast_block_log<T>(ctx->logN);
+    return !ctx->force_generic_ntt && gp::fast_supported<T>(logb) && logb == ntt_block_log<T>(ctx);
 }
 using gp::split_top;
 

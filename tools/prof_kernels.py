@@ -79,6 +79,12 @@ if __name__ == "__main__":
         ntt(1 << 14, 16, 28, 256)
     if what in ("ntt64", "all"):
         ntt(1 << 14, 8, 51, 256)
+    if what in ("ntt15",):
+        ntt(1 << 15, 8, 28, 256)
+    if what in ("ntt15w",):
+        ntt(1 << 15, 8, 51, 128)
+    if what in ("ntt16w",):
+        ntt(1 << 16, 4, 51, 128)
     if what in ("ntt16", "all"):
         ntt(1 << 16, 8, 28, 128)
     if what in ("md", "all"):
