@@ -15,6 +15,7 @@
 #include <stdint.h>
 
 #include <atomic>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -67,6 +68,8 @@ struct GpuContext {
     void *d_fwd = nullptr;   // [L][N] TwPair: psi^bitrev(i)
     void *d_inv = nullptr;   // [L][N] TwPair: psi^-bitrev(i)
     void *d_limb = nullptr;  // [L] LimbConst
+    void *d_garner = nullptr;  // [L][L] u64: q_j^-1 mod q_i (compact wire format), built on first use
+    std::mutex lazy_mutex;
     bool nocsub = false;             // forward NTT without conditional subtractions (36*qmax fits the word)
     bool force_generic_ntt = false;  // MXX_NTT_GENERIC=1: use only the runtime-planned kernels of ntt.cuh
     int ntt_block_override = 0;      // MXX_NTT_BLOCK_LOG

@@ -61,6 +61,7 @@ void free_context(GpuContext *ctx) {
     if (ctx->d_fwd) cudaFree(ctx->d_fwd);
     if (ctx->d_inv) cudaFree(ctx->d_inv);
     if (ctx->d_limb) cudaFree(ctx->d_limb);
+    if (ctx->d_garner) cudaFree(ctx->d_garner);
     for (int i = 0; i < 2; i++) {
         if (ctx->aux[i]) cudaStreamSynchronize(ctx->aux[i]);
         if (ctx->aux[i]) cudaStreamDestroy(ctx->aux[i]);

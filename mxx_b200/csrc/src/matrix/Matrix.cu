@@ -15,6 +15,7 @@
 #include "ntt.cuh"
 #include "ntt_fast.cuh"
 #include "serde.cuh"
+#include "compact.cuh"
 
 #include "MatrixCommon.inl"
 #include "MatrixData.inl"
@@ -22,4 +23,5 @@
 #include "MatrixNTT.inl"
 #include "MatrixArith.inl"
 #include "MatrixDecompose.inl"
+#include "MatrixCompact.inl"
 #include "MatrixDeferred.inl"

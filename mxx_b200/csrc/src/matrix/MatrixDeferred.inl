@@ -1,5 +1,5 @@
 // MatrixDeferred.inl — symbols of the reference ABI that are outside the hot path
-// (SURVEY §8f "next" rows: samplers, trapdoor perturbation, compact wire format).  They
+// (SURVEY §8f "next" rows: samplers, trapdoor perturbation).  They
 // are exported so the Rust crate links against this library unchanged; each fails loudly
 // (non-zero + message) rather than falling back to any CPU path.
 // Reference implementations: cuda/src/matrix/MatrixSampling.cu, MatrixTrapdoor.cu,
@@ -7,12 +7,6 @@
 
 #define GP_NOT_BUILT(name) return gp::set_error(name ": not built in this library yet (outside the DCRT matrix-mul hot path)")
 
-extern "C" int gpu_matrix_store_compact_bytes(GpuMatrix *, uint8_t *, size_t, uint16_t *, uint16_t *, size_t *) {
-    GP_NOT_BUILT("gpu_matrix_store_compact_bytes");
-}
-extern "C" int gpu_matrix_load_compact_bytes(GpuMatrix *, const uint8_t *, size_t, uint16_t) {
-    GP_NOT_BUILT("gpu_matrix_load_compact_bytes");
-}
 extern "C" int gpu_matrix_gauss_samp_gq_arb_base(GpuMatrix *, uint32_t, double, double, GpuRngSeed, GpuMatrix *) {
     GP_NOT_BUILT("gpu_matrix_gauss_samp_gq_arb_base");
 }

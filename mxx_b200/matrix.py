@@ -27,6 +27,27 @@ def mul_decompose_column_chunk_width() -> int:
         return 1
 
 
+
+def _varint(v: int) -> bytes:
+    """bincode 2 standard config: unsigned varint (u16/u32/u64/usize)"""
+    v = int(v)
+    if v < 251:
+        return bytes([v])
+    if v < 1 << 16:
+        return bytes([251]) + v.to_bytes(2, "little")
+    if v < 1 << 32:
+        return bytes([252]) + v.to_bytes(4, "little")
+    return bytes([253]) + v.to_bytes(8, "little")
+
+
+def _unvarint(data: bytes, pos: int):
+    t = data[pos]
+    if t < 251:
+        return t, pos + 1
+    width = {251: 2, 252: 4, 253: 8}[t]
+    return int.from_bytes(data[pos + 1: pos + 1 + width], "little"), pos + 1 + width
+
+
 class PinnedBuffer:
     """Page-locked host buffer from gpu_pinned_alloc (gpu.rs:236-237), viewed as numpy uint64."""
 
@@ -207,6 +228,59 @@ class GpuDCRTPolyMatrix:
                      "gpu_matrix_store_const_coeff_batch", self._L)
         self._wait(ev, "store_const")
         return words
+
+    # -- compact wire format (gpu_dcrt_poly.rs:956-1044, 1681-1712) -----------------------------------
+    def to_compact_bytes(self) -> bytes:
+        """into_compact_bytes on a clone (the native call converts an EVAL matrix to coefficient form in
+        place, MatrixSerde.cu:1108-1115; the Rust method consumes `self`).  Envelope: bincode standard config of
+        (1u8, format u8, level u32, nrow, ncol, max_coeff_bits u16, bytes_per_coeff u16, payload)."""
+        src = self.clone()
+        n = self.params.ring_dimension
+        count = self.nrow * self.ncol * n
+        bits_upper = sum(q.bit_length() for q in self.params.moduli[: self.level + 1])
+        capacity = (count * bits_upper + 7) // 8
+        buf = (C.c_uint8 * max(capacity, 1))()
+        mb, bpc, plen = C.c_uint16(0), C.c_uint16(0), C.c_size_t(0)
+        check_status(self._L.gpu_matrix_store_compact_bytes(src.raw, buf, capacity, C.byref(mb), C.byref(bpc), C.byref(plen)),
+                     "gpu_matrix_store_compact_bytes", self._L)
+        payload = bytes(buf[: plen.value])
+        fmt = GPU_POLY_FORMAT_EVAL if self.is_ntt else GPU_POLY_FORMAT_COEFF
+        return (bytes([1, fmt]) + _varint(self.level) + _varint(self.nrow) + _varint(self.ncol) + _varint(mb.value) + _varint(bpc.value)
+                + _varint(len(payload)) + payload)
+
+    @classmethod
+    def from_compact_bytes(cls, params, data: bytes):
+        """gpu_dcrt_poly.rs:1004-1044"""
+        version, fmt = data[0], data[1]
+        assert version == 1, f"Unsupported compact matrix version: {version}"
+        assert fmt in (GPU_POLY_FORMAT_COEFF, GPU_POLY_FORMAT_EVAL), f"Invalid compact matrix format tag: {fmt}"
+        pos = 2
+        level, pos = _unvarint(data, pos)
+        nrow, pos = _unvarint(data, pos)
+        ncol, pos = _unvarint(data, pos)
+        max_bits, pos = _unvarint(data, pos)
+        bpc, pos = _unvarint(data, pos)
+        plen, pos = _unvarint(data, pos)
+        payload = data[pos: pos + plen]
+        assert len(payload) == plen, "truncated compact payload"
+        assert level < params.crt_depth, f"invalid compact matrix level: {level}"
+        assert bpc == (max_bits + 7) // 8, f"compact bytes_per_coeff mismatch: got {bpc}, expected {(max_bits + 7) // 8}"
+        out = cls(params, nrow, ncol, level, False)
+        buf = (C.c_uint8 * max(plen, 1)).from_buffer_copy(payload if plen else b"\0")
+        check_status(out._L.gpu_matrix_load_compact_bytes(out.raw, buf, plen, max_bits), "gpu_matrix_load_compact_bytes", out._L)
+        out.is_ntt = False
+        if fmt == GPU_POLY_FORMAT_EVAL:
+            out.ntt_in_place()
+        return out
+
+    @staticmethod
+    def zero_compact_bytes(params, nrow, ncol, level, is_ntt, max_coeff_bits) -> bytes:
+        """gpu_dcrt_poly.rs:1681-1712"""
+        assert level < params.crt_depth, "invalid level for compact zero matrix"
+        mb = max(int(max_coeff_bits), 1)
+        plen = (nrow * ncol * params.ring_dimension * mb + 7) // 8
+        fmt = GPU_POLY_FORMAT_EVAL if is_ntt else GPU_POLY_FORMAT_COEFF
+        return bytes([1, fmt]) + _varint(level) + _varint(nrow) + _varint(ncol) + _varint(mb) + _varint((mb + 7) // 8) + _varint(plen) + bytes(plen)
 
     # -- shape / domain --------------------------------------------------------------------
     def size(self):

@@ -210,3 +210,51 @@ def negacyclic_schoolbook(a: np.ndarray, b: np.ndarray, q: int) -> np.ndarray:
     c = np.empty_like(a)
     lib().orc_negacyclic_schoolbook(_p(a), _p(b), _p(c), a.size, q)
     return c
+
+
+# -- compact wire format (pure-Python big integers; small cases only) --------------------------
+def compact_encode(coeff_rns: np.ndarray, moduli) -> tuple[int, bytes]:
+    """Restates gpu_poly_store_compact_bytes (cuda/src/matrix/MatrixSerde.cu:1066-1630) on a COEFFICIENT-form
+    matrix (nrow, ncol, limbs, n): CRT-reconstruct every coefficient to X in [0, Q) (kernel :162-278),
+    centre it — negative iff X > floor(Q/2), magnitude Q - X (:280-338) — and pack B = max magnitude width + 1
+    bits per coefficient, LSB first, the sign in bit B-1 (:340-386); B = 0 when everything is zero (:1552).
+    Returns (B, payload)."""
+    m = np.ascontiguousarray(coeff_rns, dtype=np.uint64)
+    nrow, ncol, L, n = m.shape
+    qs = [int(q) for q in moduli[:L]]
+    Q = 1
+    for q in qs:
+        Q *= q
+    basis = [(Q // q) * pow(Q // q, -1, q) for q in qs]
+    half = Q >> 1
+    vals = []
+    flat = m.reshape(nrow * ncol, L, n)
+    for p in range(flat.shape[0]):
+        for j in range(n):
+            X = sum(int(flat[p, l, j]) * basis[l] for l in range(L)) % Q
+            vals.append((1, Q - X) if X > half else (0, X))
+    width = max((mag.bit_length() for _, mag in vals), default=0)
+    if width == 0:
+        return 0, b""
+    B = width + 1
+    acc = 0
+    for k, (neg, mag) in enumerate(vals):
+        acc |= (mag | (neg << (B - 1))) << (k * B)
+    return B, acc.to_bytes((len(vals) * B + 7) // 8, "little")
+
+
+def compact_decode(payload: bytes, B: int, nrow: int, ncol: int, moduli, n: int) -> np.ndarray:
+    """Restates gpu_poly_load_compact_bytes / serde_unpack_packed_coeffs_mod_kernel (MatrixSerde.cu:388-470, 1632-1944):
+    residues of the signed coefficient in every limb, coefficient form."""
+    L = len(moduli)
+    out = np.zeros((nrow * ncol, L, n), dtype=np.uint64)
+    if B:
+        acc = int.from_bytes(payload, "little")
+        mask = (1 << (B - 1)) - 1
+        for k in range(nrow * ncol * n):
+            v = (acc >> (k * B)) & ((1 << B) - 1)
+            mag, neg = v & mask, v >> (B - 1)
+            for l, q in enumerate(moduli):
+                r = mag % int(q)
+                out[k // n, l, k % n] = (int(q) - r) % int(q) if neg else r
+    return out.reshape(nrow, ncol, L, n)
