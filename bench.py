@@ -298,6 +298,59 @@ def bench_mul_decompose(device, steps, warmup, hbm_peak, ip=None):
     return res
 
 
+def bench_bgg_chain(dist, device, depth_gates=8):
+    """configs[3] (C4): depth-8 chain of BGG+ encoding products at n = 2^15 (L = 8 x 51-bit, base 2^17, d = 1), the
+    columns of every right operand sharded over the ranks; per gate one fused mul_decompose on the local columns
+    (no collective) and ONE all-gather of the stacked (1 + d) x m block (mxx_b200/bgg.py, mxx_b200/dist.py).
+    The encoding relation c = s*A - x*(s*G) is checked on the final encoding (exact, error-free inputs)."""
+    from mxx_b200 import GpuDCRTPolyMatrix, GpuDCRTPolyParams, standard_moduli
+    from mxx_b200.bgg import BggEncoding, BggPublicKey, ShardedBggEvaluator, encode
+    from mxx_b200.dist import ColumnShardedOps, ColumnShards
+
+    n, Lm, bits, bb, d = 1 << 15, 8, 51, 17, 1
+    moduli = standard_moduli(n, Lm, bits)
+    params = GpuDCRTPolyParams(n, moduli, bb, gpu_ids=(device,))
+    ell = params.modulus_digits()
+    m = d * ell
+    ops = ColumnShardedOps(params) if dist.world > 1 else None
+
+    def rnd(rows, cols, seed):
+        h = np.empty((rows, cols, Lm, n), dtype=np.uint64)
+        uniform_host(h, moduli, seed=seed)
+        return GpuDCRTPolyMatrix.from_rns(params, h, True)
+
+    gadget = GpuDCRTPolyMatrix.gadget_matrix(params, d)
+    secret = rnd(1, d, 0x6D7878_0200)
+    left = encode(secret, BggPublicKey(rnd(d, m, 0x6D7878_0201)), rnd(1, 1, 0x6D7878_0202), gadget)
+    right = encode(secret, BggPublicKey(rnd(d, m, 0x6D7878_0203)), rnd(1, 1, 0x6D7878_0204), gadget)
+    sh = ColumnShards(m, dist.world)
+    c0, c1 = sh.range(dist.rank)
+    r_vec_local, r_pk_local = right.vector.slice_columns(c0, c1), right.pubkey.matrix.slice_columns(c0, c1)
+    ev = ShardedBggEvaluator(ops) if ops else None
+
+    def gate(acc):
+        if ev:
+            return ev.mul_gate(acc, r_vec_local, r_pk_local, right.plaintext, m)
+        return acc.mul(right, fused=True)
+
+    acc = gate(left)  # warm-up (NCCL communicator, pools)
+    params.synchronize()
+    dist.barrier()
+    t0 = time.perf_counter()
+    acc = left
+    for _ in range(depth_gates):
+        acc = gate(acc)
+    params.synchronize()
+    dt = dist.max(time.perf_counter() - t0)
+    ok = acc.vector == secret * acc.pubkey.matrix - (secret * gadget).mul_scalar(acc.plaintext)
+    logn = 15
+    per_gate_bfly = (d * m * Lm + m * m * Lm) * (n // 2) * logn
+    return {"workload": "C4 BGG+ encoding-product chain, n=2^15, L=8x51-bit, bb=17 (ell=24), d=1, depth 8; right-operand columns sharded over the ranks",
+            "gates": depth_gates, "ms_per_gate": round(dt * 1e3 / depth_gates, 4), "gates_per_s": round(depth_gates / dt, 2),
+            "butterflies_per_gate": per_gate_bfly, "exchange": "one all_gather of the (1+d) x m block per gate" if ev else "none (1 rank)",
+            "relation_holds": bool(ok), "timing": "host clock around the chain with a stream synchronize and barrier on both sides, max over ranks"}
+
+
 def int_peaks():
     """Register-resident microbenchmark of the butterfly / MAC primitives (tools/modmul_peak.cu): the measured
     INT-issue roofline denominators (butterflies/s, MACs/s) for the compute-bound kernels."""
@@ -449,6 +502,8 @@ def run_gpu(args):
     }
     if assemble:
         line["assemble"] = assemble
+    if not args.no_extras:
+        line["bgg_chain"] = bench_bgg_chain(dist, device)
 
     if dist.rank == 0 and dist.world == 1:
         # CPU baseline beside it: same operands, all host threads, and a parity check of the GPU result
@@ -470,7 +525,7 @@ def run_gpu(args):
             line["ntt"] = bench_ntt(device, max(3, min(args.steps, 20)), args.warmup, hbm_peak, ip)
             line["mul_decompose"] = bench_mul_decompose(device, max(3, min(args.steps, 20)), args.warmup, hbm_peak, ip)
     if dist.rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     dist.close()
 
 
@@ -510,10 +565,28 @@ def run_reference(args):
                                        "the reference's own OpenFHE path is unavailable on this box)"},
             "e2e": {"value": v, "unit": "matrix-muls/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_REAL_STDOUT = None
+
+
+def emit(line: dict) -> None:
+    """the ONE JSON line goes to the process's real stdout; everything else any library prints (NCCL's version
+    banner, torchrun notices) has been routed to stderr by main()"""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
 
 
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)  # fd 1 -> stderr for the duration of the run
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)
