@@ -107,6 +107,15 @@ class ColumnShardedOps:
         self.group = group
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self._ext = None
+
+    def _stream(self):
+        """the context's CUDA stream as a torch stream: collectives issued under it are ordered with the
+        library's kernels on the device (NCCL's own stream waits on / is waited on by events), no host sync"""
+        torch, _ = _torch()
+        if self._ext is None:
+            self._ext = torch.cuda.ExternalStream(self.params.stream(), device=f"cuda:{self.params.gpu_ids[0]}")
+        return torch.cuda.stream(self._ext)
 
     def shards(self, ncol: int) -> ColumnShards:
         return ColumnShards(ncol, self.world)
@@ -136,10 +145,9 @@ class ColumnShardedOps:
             send = GpuDCRTPolyMatrix(p, local.nrow, width, level=local.level, is_ntt=local.is_ntt)
             send.copy_block_from(local, 0, 0, 0, 0, local.nrow, local.ncol)
         recv = [GpuDCRTPolyMatrix(p, local.nrow, width, level=local.level, is_ntt=local.is_ntt) for _ in range(self.world)]
-        p.synchronize()  # the context stream produced `send`; NCCL runs on torch's stream
         tensors = [device_tensor(m) for m in recv]
-        dist.all_gather(tensors, device_tensor(send), group=self.group)
-        torch.cuda.current_stream().synchronize()
+        with self._stream():  # ordered after the kernels that produced `send`, before the copies below
+            dist.all_gather(tensors, device_tensor(send), group=self.group)
         out = GpuDCRTPolyMatrix(p, local.nrow, ncol, level=local.level, is_ntt=local.is_ntt)
         for r, m in enumerate(recv):
             c0, c1 = sh.range(r)
@@ -152,6 +160,5 @@ class ColumnShardedOps:
         torch, dist = _torch()
         if self.world == 1:
             return
-        self.params.synchronize()
-        dist.broadcast(device_tensor(mat), src=src, group=self.group)
-        torch.cuda.current_stream().synchronize()
+        with self._stream():
+            dist.broadcast(device_tensor(mat), src=src, group=self.group)
