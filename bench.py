@@ -43,6 +43,7 @@ NTT_CASES = [  # (n, depth, bits): ~256 MiB of device residues per batch (> the 
     (1 << 14, 8, 51), (1 << 15, 8, 51), (1 << 16, 4, 51),
 ]
 NTT_BATCH_BYTES = 256 << 20
+NCU_MATMUL_TRAFFIC = 3572995000 + 98338048  # bytes per C1-R launch, measured once with ncu (profiles/r01_ncu_v5_summary.txt)
 
 
 def peaks():
@@ -495,9 +496,10 @@ def run_gpu(args):
                 "d2h_bytes_per_step": int(pinO.nbytes), "steps": e2e_steps,
                 "path": "gpu_matrix_load_rns_batch x2 (pinned host u64) -> gpu_matrix_mul -> gpu_matrix_store_rns_batch -> gpu_event_set_wait"},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "kernel": "matmul_kernel<u32,4,1,4>", "achieved": round(achieved, 1), "peak": hbm_peak,
-                     "unit": "GB/s", "frac": round(achieved / hbm_peak, 4), "traffic": None, "algorithmic_bytes": algo_bytes,
-                     "peak_source": peak_src},
+        "roofline": {"bound": "hbm", "kernel": "matmul_kernel<u32,V=4,TR=1,TC=6,unroll 2,64 threads>", "achieved": round(achieved, 1), "peak": hbm_peak,
+                     "unit": "GB/s", "frac": round(achieved / hbm_peak, 4), "traffic": NCU_MATMUL_TRAFFIC, "algorithmic_bytes": algo_bytes,
+                     "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full (profiles/r01_ncu_v5_summary.txt)",
+                     "peak_source": peak_src + "; a copy moves read+write, this kernel is 97% reads, so a fraction slightly above 1 is expected"},
         "clocks": clk.summary(),
     }
     if assemble:
