@@ -122,6 +122,15 @@ int gpu_matrix_sample_distribution_columns(GpuMatrix *out, int dist_type, double
  * (src/matrix/gpu_dcrt_poly.rs:1414-1493).  lhs EVAL; rhs EVAL or COEFF; out EVAL.
  * small != 0 selects mul_decompose_small (gpu_dcrt_poly.rs:1495-1574). */
 int gpu_matrix_mul_decompose(GpuMatrix *out, const GpuMatrix *lhs, const GpuMatrix *rhs, uint32_t base_bits, int small);
+/* Big-integer coefficients <-> residues ON THE DEVICE: the conversion step either side of the path
+ * (SURVEY 8f-4).  words[(poly * n + j) * words_per_coeff + w], little-endian u64 words of the coefficient.
+ * load: every active limb receives the coefficient mod q_limb — the host BigUint `%` loop of
+ *   GpuDCRTPolyMatrix::from_cpu_matrix (src/matrix/gpu_dcrt_poly.rs:793-803) and GpuDCRTPoly::from_coeffs
+ *   (src/poly/dcrt/gpu.rs:903-920); `format` tags the data (EVAL: natural slot order, as load_rns_batch).
+ * store: CRT reconstruction to [0, Q), Q = product of the active moduli — the host loop of
+ *   GpuDCRTPoly::coeffs (gpu.rs:959-994); requires coefficient form. */
+int gpu_matrix_load_bigint_batch(GpuMatrix *mat, const uint64_t *words, size_t words_per_coeff, int format, GpuEventSet **out_events);
+int gpu_matrix_store_bigint_batch(const GpuMatrix *mat, uint64_t *words_out, size_t words_per_coeff, GpuEventSet **out_events);
 /* The CUDA stream (cudaStream_t) all work of this context is ordered on; for CUDA-event timing. */
 void *gpu_context_stream(const GpuContext *ctx);
 /* Device pointer / word size (4 or 8) / format of a matrix's storage, [poly][limb][coeff]. */

@@ -28,7 +28,8 @@ template <typename T> GP_HD uint64_t cmul(uint64_t a, uint64_t b, const LimbCons
 
 // Pass 1: residues -> centred magnitude words (scratch[k][words]) + sign byte; max bit width by atomicMax.
 // garner[j * limbs_total + i] = q_j^-1 mod q_i (j < i); qwords / hwords = Q and floor(Q/2), little endian.
-template <typename T, int WMAX>
+// CENTRE = false keeps X itself (big-integer store): no sign, no width.
+template <typename T, int WMAX, bool CENTRE = true>
 __global__ void compact_reconstruct_kernel(const T *__restrict__ data, CompactGeom g, const LimbConst<T> *__restrict__ lc,
                                            const uint64_t *__restrict__ garner, uint32_t garner_stride,
                                            const uint64_t *__restrict__ qwords, const uint64_t *__restrict__ hwords,
@@ -67,7 +68,7 @@ __global__ void compact_reconstruct_kernel(const T *__restrict__ data, CompactGe
         // centre: negative iff X > floor(Q/2)
         int cmp = 0;
         for (int w = (int)g.words - 1; w >= 0 && cmp == 0; w--) cmp = X[w] > hwords[w] ? 1 : (X[w] < hwords[w] ? -1 : 0);
-        const bool neg = cmp > 0;
+        const bool neg = CENTRE && cmp > 0;
         if (neg) {
             uint64_t borrow = 0;
             for (uint32_t w = 0; w < g.words; w++) {
@@ -83,11 +84,11 @@ __global__ void compact_reconstruct_kernel(const T *__restrict__ data, CompactGe
                 break;
             }
         for (uint32_t w = 0; w < g.words; w++) mag[k * g.words + w] = X[w];
-        sign[k] = neg ? 1 : 0;
+        if (CENTRE) sign[k] = neg ? 1 : 0;
     }
     // one atomic per warp
     for (int o = 16; o; o >>= 1) width = max(width, __shfl_xor_sync(0xffffffffu, width, o));
-    if ((threadIdx.x & 31) == 0 && width) atomicMax(max_bits, width);
+    if (CENTRE && (threadIdx.x & 31) == 0 && width) atomicMax(max_bits, width);
 }
 
 // Pass 2: scatter B = bits per coefficient into the (zeroed, 8-byte padded) payload.
@@ -164,6 +165,33 @@ __global__ void compact_unpack_kernel(T *__restrict__ data, CompactGeom g, const
             r = r >= q ? r - q : r;
         }
         if (neg && r) r = q - r;
+        p[(size_t)i << g.logn] = (T)r;
+    }
+}
+
+// Big-integer coefficients -> residues (the host loop `value % modulus` of
+// GpuDCRTPolyMatrix::from_cpu_matrix, src/matrix/gpu_dcrt_poly.rs:793-803, and of GpuDCRTPoly::from_coeffs,
+// src/poly/dcrt/gpu.rs:903-920, moved onto the device).  words[(poly * n + j) * wpc + w], little endian;
+// BITREV: the input is EVAL data in natural slot order, the device keeps it bit-reversed.
+template <typename T, bool BITREV>
+__global__ void bigint_load_kernel(T *__restrict__ data, CompactGeom g, const LimbConst<T> *__restrict__ lc,
+                                   const uint64_t *__restrict__ words, uint32_t wpc) {
+    const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= g.count) return;
+    const size_t n = (size_t)1 << g.logn, poly = k >> g.logn;
+    const uint32_t j = (uint32_t)(k & (n - 1));
+    const uint32_t slot = BITREV ? (g.logn ? brev32(j) >> (32 - g.logn) : 0u) : j;
+    T *p = data + ((poly * g.limbs) << g.logn) + slot;
+    const uint64_t *src = words + k * wpc;
+    for (uint32_t i = 0; i < g.limbs; i++) {
+        const LimbConst<T> c = lc[i];
+        const uint64_t q = (uint64_t)c.q;
+        uint64_t r = 0;
+        for (int w = (int)wpc - 1; w >= 0; w--) {  // r = (r * 2^64 + word) mod q
+            r = cmul<T>(r, (uint64_t)c.r64, c);
+            r += (uint64_t)red64<T>(src[w], c);
+            r = r >= q ? r - q : r;
+        }
         p[(size_t)i << g.logn] = (T)r;
     }
 }

@@ -162,3 +162,76 @@ extern "C" int gpu_matrix_load_compact_bytes(GpuMatrix *mat, const uint8_t *payl
     if (bind_device(ctx)) return 1;
     return GP_DISPATCH_WIDTH(ctx, return run_compact_load<T>(ctx, mat, payload, payload_len, max_coeff_bits););
 }
+
+// ---- extension: big-integer coefficients <-> residues on the device ------------------------------
+// Replaces the per-coefficient BigUint `%` of GpuDCRTPolyMatrix::from_cpu_matrix (gpu_dcrt_poly.rs:793-803) /
+// GpuDCRTPoly::from_coeffs (gpu.rs:903-920) and the host CRT reconstruction of GpuDCRTPoly::coeffs (gpu.rs:959-994).
+extern "C" int gpu_matrix_load_bigint_batch(GpuMatrix *mat, const uint64_t *words, size_t words_per_coeff, int format,
+                                            GpuEventSet **out_events) {
+    if (!mat || !mat->ctx || !out_events) return gp::set_error("invalid gpu_matrix_load_bigint_batch arguments");
+    *out_events = nullptr;
+    if (format != GPU_POLY_FORMAT_COEFF && format != GPU_POLY_FORMAT_EVAL) return gp::set_error("invalid format in gpu_matrix_load_bigint_batch");
+    GpuContext *ctx = mat->ctx;
+    const size_t count = mat->polys() << ctx->logN;
+    mat->format = format;
+    if (count == 0 || mat->level < 0) return 0;
+    if (!words || words_per_coeff == 0) return gp::set_error("null words in gpu_matrix_load_bigint_batch");
+    if (bind_device(ctx)) return 1;
+    cudaStream_t st = ctx->stream;
+    Scratch dev;
+    if (dev.alloc(count * words_per_coeff * sizeof(uint64_t), st)) return 1;
+    GP_CUDA(cudaMemcpyAsync(dev.p, words, count * words_per_coeff * sizeof(uint64_t), cudaMemcpyHostToDevice, st), "cudaMemcpyAsync(bigint H2D)");
+    gp::CompactGeom g{(uint32_t)mat->limbs(), (uint32_t)ctx->logN, 0, count};
+    const unsigned threads = 128, grid = (unsigned)((count + threads - 1) / threads);
+    int stt = GP_DISPATCH_WIDTH(
+        ctx, const auto *lc = (const gp::LimbConst<T> *)ctx->d_limb;
+        if (format == GPU_POLY_FORMAT_EVAL)
+            gp::bigint_load_kernel<T, true><<<grid, threads, 0, st>>>((T *)mat->data, g, lc, (const uint64_t *)dev.p, (uint32_t)words_per_coeff);
+        else
+            gp::bigint_load_kernel<T, false><<<grid, threads, 0, st>>>((T *)mat->data, g, lc, (const uint64_t *)dev.p, (uint32_t)words_per_coeff);
+        gp::count_launch(); GP_CHECK_LAUNCH("bigint_load_kernel"); return 0;);
+    if (stt) return stt;
+    return make_event_set(ctx, out_events);
+}
+
+// words_out[(poly * n + j) * words_per_coeff + w]: the coefficient in [0, Q) (Q = product of the active moduli);
+// requires coefficient form (as GpuDCRTPoly::coeffs converts first); words_per_coeff >= ceil(bits(Q) / 64).
+extern "C" int gpu_matrix_store_bigint_batch(const GpuMatrix *mat, uint64_t *words_out, size_t words_per_coeff, GpuEventSet **out_events) {
+    if (!mat || !mat->ctx || !out_events) return gp::set_error("invalid gpu_matrix_store_bigint_batch arguments");
+    *out_events = nullptr;
+    GpuContext *ctx = mat->ctx;
+    const size_t count = mat->polys() << ctx->logN;
+    if (count == 0 || mat->level < 0) return 0;
+    if (mat->format != GPU_POLY_FORMAT_COEFF) return gp::set_error("gpu_matrix_store_bigint_batch requires coeff format");
+    if (!words_out) return gp::set_error("null words_out in gpu_matrix_store_bigint_batch");
+    const size_t limbs = mat->limbs(), words = compact_words(ctx, limbs);
+    if (words_per_coeff < words) return gp::set_error("words_per_coeff too small in gpu_matrix_store_bigint_batch");
+    if (words > (size_t)gp::kCompactMaxWords) return gp::set_error("words_per_coeff exceeds kernel limit in gpu_matrix_store_bigint_batch");
+    if (bind_device(ctx)) return 1;
+    if (ensure_garner(ctx)) return 1;
+    cudaStream_t st = ctx->stream;
+    std::vector<uint64_t> q = modulus_words(ctx, limbs, words);
+    Scratch consts, mag;
+    if (consts.alloc(2 * words * sizeof(uint64_t), st) || mag.alloc(count * words * sizeof(uint64_t), st)) return 1;
+    std::vector<uint64_t> both(q);
+    both.insert(both.end(), q.begin(), q.end());
+    GP_CUDA(cudaMemcpyAsync(consts.p, both.data(), both.size() * sizeof(uint64_t), cudaMemcpyHostToDevice, st), "cudaMemcpyAsync(Q)");
+    GP_CUDA(cudaStreamSynchronize(st), "cudaStreamSynchronize(Q)");  // `both` is a stack object
+    gp::CompactGeom g{(uint32_t)limbs, (uint32_t)ctx->logN, (uint32_t)words, count};
+    const unsigned threads = 128, grid = (unsigned)((count + threads - 1) / threads);
+    const uint64_t *qw = (const uint64_t *)consts.p;
+    int stt = GP_DISPATCH_WIDTH(
+        ctx, const auto *lc = (const gp::LimbConst<T> *)ctx->d_limb;
+        if (limbs <= 8 && words <= 8)
+            gp::compact_reconstruct_kernel<T, 8, false><<<grid, threads, 0, st>>>((const T *)mat->data, g, lc, (const uint64_t *)ctx->d_garner,
+                (uint32_t)ctx->moduli.size(), qw, qw + words, (uint64_t *)mag.p, nullptr, nullptr);
+        else
+            gp::compact_reconstruct_kernel<T, gp::kCompactMaxWords, false><<<grid, threads, 0, st>>>((const T *)mat->data, g, lc,
+                (const uint64_t *)ctx->d_garner, (uint32_t)ctx->moduli.size(), qw, qw + words, (uint64_t *)mag.p, nullptr, nullptr);
+        gp::count_launch(); GP_CHECK_LAUNCH("compact_reconstruct_kernel"); return 0;);
+    if (stt) return stt;
+    if (words_per_coeff > words) std::fill_n(words_out, count * words_per_coeff, (uint64_t)0);
+    GP_CUDA(cudaMemcpy2DAsync(words_out, words_per_coeff * 8, mag.p, words * 8, words * 8, count, cudaMemcpyDeviceToHost, st),
+            "cudaMemcpy2DAsync(bigint D2H)");
+    return make_event_set(ctx, out_events);
+}

@@ -229,6 +229,48 @@ class GpuDCRTPolyMatrix:
         self._wait(ev, "store_const")
         return words
 
+    # -- big-integer coefficients (device-side conversion, extension) ------------------------
+    @classmethod
+    def from_biguints(cls, params, values, nrow: int, ncol: int, is_ntt: bool = True, level: int | None = None):
+        """from_cpu_matrix / from_coeffs (gpu_dcrt_poly.rs:769-817, gpu.rs:903-920) with the `value % modulus`
+        loop done on the device: `values` = nrow*ncol*n Python ints (row-major polys, natural coefficient /
+        slot order), any non-negative size."""
+        n = params.ring_dimension
+        vals = [int(v) for v in values]
+        assert len(vals) == nrow * ncol * n and all(v >= 0 for v in vals)
+        wpc = max(1, (max((v.bit_length() for v in vals), default=1) + 63) // 64)
+        words = np.zeros((len(vals), wpc), dtype=np.uint64)
+        mask = (1 << 64) - 1
+        for i, v in enumerate(vals):
+            for w in range(wpc):
+                words[i, w] = (v >> (64 * w)) & mask
+        out = cls(params, nrow, ncol, level, is_ntt)
+        ev = C.c_void_p()
+        check_status(out._L.gpu_matrix_load_bigint_batch(out.raw, words.ctypes.data_as(ffi.u64p), wpc, out._fmt(), C.byref(ev)),
+                     "gpu_matrix_load_bigint_batch", out._L)
+        out._wait(ev, "load_bigint")
+        return out
+
+    def to_biguints(self) -> list:
+        """coeffs() (gpu.rs:959-994) for every polynomial: CRT-reconstructed coefficients in [0, Q) as Python ints,
+        reconstructed on the device (a coefficient-form copy is made if the matrix is in the evaluation domain)."""
+        src = self
+        if self.is_ntt:
+            src = self.clone()
+            src.intt_all_in_place()
+        n = self.params.ring_dimension
+        q_bits = sum(q.bit_length() for q in self.params.moduli[: self.level + 1])
+        wpc = max(1, (q_bits + 63) // 64)
+        count = self.nrow * self.ncol * n
+        words = np.zeros((count, wpc), dtype=np.uint64)
+        if count == 0:
+            return []
+        ev = C.c_void_p()
+        check_status(self._L.gpu_matrix_store_bigint_batch(src.raw, words.ctypes.data_as(ffi.u64p), wpc, C.byref(ev)),
+                     "gpu_matrix_store_bigint_batch", self._L)
+        self._wait(ev, "store_bigint")
+        return [sum(int(words[i, w]) << (64 * w) for w in range(wpc)) for i in range(count)]
+
     # -- compact wire format (gpu_dcrt_poly.rs:956-1044, 1681-1712) -----------------------------------
     def to_compact_bytes(self) -> bytes:
         """into_compact_bytes on a clone (the native call converts an EVAL matrix to coefficient form in

@@ -119,3 +119,38 @@ def test_compact_side_by_side_with_reference_library(n, depth, bits, bb):
         theirs = mx.GpuDCRTPolyMatrix.from_rns(rparams, host, False).to_compact_bytes()
         assert ours == theirs
         assert np.array_equal(mx.GpuDCRTPolyMatrix.from_compact_bytes(rparams, ours).to_rns(), host)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,depth,bits,bb", [(16, 2, 17, 1), (64, 3, 24, 12), (128, 2, 51, 17), (256, 9, 28, 14), (64, 5, 59, 20)])
+def test_bigint_conversion_on_device(n, depth, bits, bb):
+    """BigUint coefficients -> residues and back (CRT) on the device, against Python integers"""
+    import random
+
+    mx, moduli, params, plan = _gpu(n, depth, bits, bb)
+    Q = 1
+    for q in moduli:
+        Q *= int(q)
+    rnd = random.Random(5)
+    for big in (Q, Q * Q + 12345, 1 << 40):
+        vals = [rnd.randrange(big) for _ in range(2 * 3 * n)]
+        want = np.array([[v % int(q) for v in vals] for q in moduli], dtype=np.uint64)  # [limb][poly*n]
+        want = want.reshape(depth, 6, n).transpose(1, 0, 2).reshape(2, 3, depth, n)
+        for is_ntt in (False, True):  # the tag only says which domain the caller's numbers live in
+            g = mx.GpuDCRTPolyMatrix.from_biguints(params, vals, 2, 3, is_ntt=is_ntt)
+            assert g.is_ntt == is_ntt and np.array_equal(g.to_rns(), want)
+        g = mx.GpuDCRTPolyMatrix.from_biguints(params, vals, 2, 3, is_ntt=False)
+        assert g.to_biguints() == [v % Q for v in vals]
+    # evaluation-domain matrices reconstruct their COEFFICIENTS (coeffs() converts first, gpu.rs:959-961)
+    host = plan.uniform(1, 2, seed=9)
+    ge = mx.GpuDCRTPolyMatrix.from_rns(params, host, True)
+    gc = mx.GpuDCRTPolyMatrix.from_rns(params, plan.intt(host), False)
+    assert ge.to_biguints() == gc.to_biguints()
+    # lower level: only the active limbs take part
+    if depth > 1:
+        vals = [rnd.randrange(1 << 70) for _ in range(n)]
+        g = mx.GpuDCRTPolyMatrix.from_biguints(params, vals, 1, 1, is_ntt=False, level=depth - 2)
+        q_low = 1
+        for q in moduli[: depth - 1]:
+            q_low *= int(q)
+        assert g.to_biguints() == [v % q_low for v in vals]
