@@ -1,0 +1,484 @@
+// sampling.cuh — counter-based randomness and the integer samplers of the trapdoor path
+// (SURVEY §8 f-1).  Per-element functions are GP_HD so the host emulation harness
+// (src/emu.cu, tests only) can run the very same code without a GPU.
+//
+// Behaviour this file reproduces (so that a given GpuRngSeed yields the same matrix as the
+// reference's CUDA library):
+//   * random streams: ChaCha20 keyed by HChaCha20(seed, domain || stream2), block counter
+//     starting at stream0, nonce = stream1, eight u64 per block (cuda/src/ChaCha.cu:109-166);
+//   * uniform deviates u = (u64 >> 11) * 2^-53 clamped into (0,1)
+//     (cuda/src/matrix/MatrixSampling.cu:6-19);
+//   * the discrete Gaussian: Karney, "Sampling exactly from the normal distribution"
+//     (ACM TOMS 2016), algorithms H, G, P, B and the integer sampler with the iteration
+//     caps and the Box-Muller fall-back of MatrixSampling.cu:31-160;
+//   * the G-lattice sampler for q != b^k (Genise-Micciancio, EUROCRYPT 2018, alg. 2-4) with
+//     continuous perturbation, as in MatrixTrapdoor.cu:701-833.
+// The order in which deviates are drawn is part of the contract; the code organisation
+// (one register-resident stream object, one fused sample+scatter kernel per call, all RNS
+// limbs written by the thread that drew the integer) is this library's own.
+#pragma once
+#include <math.h>
+#include <stdint.h>
+
+#include "modarith.cuh"
+
+namespace gp {
+
+struct Seed256 {
+    uint64_t w[4];
+};
+
+// domain separators (ASCII tags) — one per distribution, MatrixSampling.cu:247-292,
+// MatrixTrapdoor.cu:236, 770
+constexpr uint64_t kDomUniform = 0x6f70656e66686531ULL;
+constexpr uint64_t kDomGauss = 0x6f70656e66686532ULL;
+constexpr uint64_t kDomBit = 0x6f70656e66686533ULL;
+constexpr uint64_t kDomTernary = 0x6f70656e66686534ULL;
+constexpr uint64_t kDomGadget = 0x6761646765746731ULL;
+constexpr uint64_t kDomPerturb = 0x7065727475726231ULL;
+
+constexpr int kMaxGaussDigits = 64;  // MatrixUtils.cu:1
+
+#define GP_CC_QR(a, b, c, d)                       \
+    x[a] += x[b]; x[d] ^= x[a]; x[d] = rotl(x[d], 16); \
+    x[c] += x[d]; x[b] ^= x[c]; x[b] = rotl(x[b], 12); \
+    x[a] += x[b]; x[d] ^= x[a]; x[d] = rotl(x[d], 8);  \
+    x[c] += x[d]; x[b] ^= x[c]; x[b] = rotl(x[b], 7)
+
+struct ChaChaStream {
+    uint32_t key[8];   // HChaCha20 sub-key
+    uint32_t ctr[4];   // words 12..15: 64-bit block counter (stream0), 64-bit nonce (stream1)
+    uint32_t out[16];  // current key-stream block
+    uint32_t pos;      // next u64 of `out`; 8 = exhausted
+
+    static GP_HD uint32_t rotl(uint32_t v, int n) {
+#ifdef __CUDA_ARCH__
+        return __funnelshift_l(v, v, n);
+#else
+        return (v << n) | (v >> (32 - n));
+#endif
+    }
+    // the 20-round ChaCha permutation (RFC 8439 §2.3, without the feed-forward)
+    // (kept out of line: it is reached from every draw site of the rejection samplers)
+    static __host__ __device__ __noinline__ void permute(uint32_t *x) {
+#pragma unroll
+        for (int dr = 0; dr < 10; dr++) {
+            GP_CC_QR(0, 4, 8, 12); GP_CC_QR(1, 5, 9, 13); GP_CC_QR(2, 6, 10, 14); GP_CC_QR(3, 7, 11, 15);
+            GP_CC_QR(0, 5, 10, 15); GP_CC_QR(1, 6, 11, 12); GP_CC_QR(2, 7, 8, 13); GP_CC_QR(3, 4, 9, 14);
+        }
+    }
+    static GP_HD void sigma(uint32_t *x) {
+        x[0] = 0x61707865u; x[1] = 0x3320646eu; x[2] = 0x79622d32u; x[3] = 0x6b206574u;
+    }
+    GP_HD void open(const Seed256 &seed, uint64_t stream0, uint64_t stream1, uint64_t stream2, uint64_t domain) {
+        uint32_t x[16];
+        sigma(x);
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            x[4 + 2 * i] = (uint32_t)seed.w[i];
+            x[5 + 2 * i] = (uint32_t)(seed.w[i] >> 32);
+        }
+        x[12] = (uint32_t)domain; x[13] = (uint32_t)(domain >> 32);
+        x[14] = (uint32_t)stream2; x[15] = (uint32_t)(stream2 >> 32);
+        permute(x);  // HChaCha20: first and last rows of the permuted state
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            key[i] = x[i];
+            key[4 + i] = x[12 + i];
+        }
+        ctr[0] = (uint32_t)stream0; ctr[1] = (uint32_t)(stream0 >> 32);
+        ctr[2] = (uint32_t)stream1; ctr[3] = (uint32_t)(stream1 >> 32);
+        pos = 8;
+    }
+    GP_HD void refill() {
+        uint32_t x[16];
+        sigma(x);
+#pragma unroll
+        for (int i = 0; i < 8; i++) x[4 + i] = key[i];
+#pragma unroll
+        for (int i = 0; i < 4; i++) x[12 + i] = ctr[i];
+        permute(x);
+        out[0] = x[0] + 0x61707865u; out[1] = x[1] + 0x3320646eu; out[2] = x[2] + 0x79622d32u; out[3] = x[3] + 0x6b206574u;
+#pragma unroll
+        for (int i = 0; i < 8; i++) out[4 + i] = x[4 + i] + key[i];
+#pragma unroll
+        for (int i = 0; i < 4; i++) out[12 + i] = x[12 + i] + ctr[i];
+        if (++ctr[0] == 0) ++ctr[1];
+        pos = 0;
+    }
+    GP_HD uint64_t next() {
+        if (pos >= 8) refill();
+        const uint64_t v = (uint64_t)out[2 * pos] | ((uint64_t)out[2 * pos + 1] << 32);
+        pos++;
+        return v;
+    }
+    // uniform deviate in the open interval (0,1), 53 bits
+    GP_HD double unit() {
+        const double scale = 1.0 / 9007199254740992.0;
+        double u = (double)(next() >> 11) * scale;
+        if (u <= 0.0) u = scale;
+        else if (u >= 1.0) u = 1.0 - scale;
+        return u;
+    }
+    // uniform residue in [0, q): rejection below the largest multiple of q
+    GP_HD uint64_t below(uint64_t q) {
+        if (q == 0) return 0;
+        const uint64_t lim = ~0ULL - (~0ULL % q);
+        for (;;) {
+            const uint64_t v = next();
+            if (v < lim) return v % q;
+        }
+    }
+    // Box-Muller (only the fall-back of the integer sampler and the continuous perturbation)
+    GP_HD double normal() {
+        const double u1 = unit();
+        const double u2 = unit();
+        const double r = sqrt(-2.0 * log(u1));
+        const double theta = 6.283185307179586476925286766559 * u2;
+        return r * cos(theta);
+    }
+};
+
+// z mod q for a signed 64-bit z
+GP_HD uint64_t signed_residue(int64_t z, uint64_t q) {
+    if (z >= 0) return (uint64_t)z % q;
+    const uint64_t mag = (uint64_t)(-(z + 1)) + 1;
+    const uint64_t r = mag % q;
+    return r == 0 ? 0 : q - r;
+}
+
+// centred representative of x mod q in (-q/2, q/2]
+GP_HD int64_t centred(uint64_t x, uint64_t q) {
+    const uint64_t r = x % q;
+    return r <= (q >> 1) ? (int64_t)r : -(int64_t)(q - r);
+}
+
+// ---- Karney's exact discrete Gaussian --------------------------------------------------
+// H: true with probability exp(-1/2)
+GP_HD bool karney_h(ChaChaStream &g) {
+    double a = g.unit();
+    if (!(a < 0.5)) return true;
+    for (;;) {
+        const double b = g.unit();
+        if (!(b < a)) return false;
+        a = g.unit();
+        if (!(a < b)) return true;
+    }
+}
+// G: k >= 0 with probability exp(-k/2)(1 - exp(-1/2)); capped like the reference
+GP_HD int32_t karney_g(ChaChaStream &g) {
+    int32_t k = 0;
+    while (karney_h(g)) {
+        if (++k > 1024) break;
+    }
+    return k;
+}
+// P: true with probability exp(-n/2)
+GP_HD bool karney_p(ChaChaStream &g, int32_t n) {
+    while (n-- && karney_h(g)) {
+    }
+    return n < 0;
+}
+// B: true with probability exp(-x(2k+x)/(2k+2))
+GP_HD bool karney_b(ChaChaStream &g, int32_t k, double x) {
+    const double m = (double)(2 * k + 2);
+    double y = x;
+    int32_t n = 0;
+    for (;; ++n) {
+        const double z = g.unit();
+        if (!(z < y)) break;
+        const double r = g.unit();
+        if (!(r < (2.0 * (double)k + x) / m)) break;
+        y = z;
+        if (n > 4096) break;
+    }
+    return (n & 1) == 0;
+}
+
+// integer z ~ D_{Z, stddev, mean}
+GP_HD int64_t karney_integer(ChaChaStream &g, double mean, double stddev) {
+    if (!(stddev > 0.0) || !isfinite(mean) || !isfinite(stddev)) return (int64_t)llround(mean);
+    const int64_t span = (int64_t)ceil(stddev);
+    if (span <= 0) return (int64_t)llround(mean);
+    for (int tries = 0; tries < (1 << 16); ++tries) {
+        const int32_t k = karney_g(g);
+        if (!karney_p(g, k * (k - 1))) continue;
+        const int64_t s = (g.next() & 1ULL) ? 1 : -1;
+        const double di0 = stddev * (double)k + (double)s * mean;
+        const int64_t i0 = (int64_t)ceil(di0);
+        const double x0 = ((double)i0 - di0) / stddev;
+        const int64_t j = (int64_t)(g.next() % (uint64_t)span);
+        const double x = x0 + (double)j / stddev;
+        if (!(x < 1.0) || (x == 0.0 && s < 0 && k == 0)) continue;
+        int32_t h = k + 1;
+        while (h-- > 0 && karney_b(g, k, x)) {
+        }
+        if (h >= 0) continue;
+        return s * (i0 + j);
+    }
+    return (int64_t)llround(mean + stddev * g.normal());
+}
+
+// ---- one coefficient of gpu_matrix_sample_distribution ----------------------------------
+enum { kDistUniform = 0, kDistGauss = 1, kDistBit = 2, kDistTernary = 3 };  // Matrix.cuh:21-27
+
+// The integer behind a Gauss / bit / ternary coefficient is the same in every RNS limb (the
+// stream is keyed by (poly, coeff) only), so it is drawn once and reduced per limb.
+GP_HD int64_t draw_small_integer(const Seed256 &seed, int dist, double sigma, uint64_t global_poly, uint64_t coeff) {
+    ChaChaStream g;
+    if (dist == kDistGauss) {
+        g.open(seed, global_poly + 1, coeff + 1, 0, kDomGauss);
+        return karney_integer(g, 0.0, sigma);
+    }
+    if (dist == kDistBit) {
+        g.open(seed, global_poly + 1, coeff + 1, 0, kDomBit);
+        return (int64_t)(g.next() & 1ULL);
+    }
+    g.open(seed, global_poly + 1, coeff + 1, 0, kDomTernary);
+    const uint64_t pick = g.next() % 3ULL;
+    return pick == 0 ? 0 : (pick == 1 ? 1 : -1);
+}
+GP_HD uint64_t draw_uniform_residue(const Seed256 &seed, uint64_t global_poly, uint64_t coeff, uint32_t limb, uint64_t q) {
+    ChaChaStream g;
+    g.open(seed, global_poly + 1, coeff + 1, (uint64_t)limb + 1, kDomUniform);
+    return g.below(q);
+}
+
+// ---- G-lattice sampler, one (poly, coeff, tower) --------------------------------------
+// Writes the dpt signed digits x with  sum_i x_i b^i == value (mod q)  and x ~ D_{Lambda, c}.
+// DMAX bounds the local arrays (8 covers every base >= ceil(crt_bits/8); 64 is the ABI limit).
+template <int DMAX>
+GP_HD void gq_sample_digits(const Seed256 &seed, uint64_t value, uint64_t q, uint32_t base_bits, uint32_t dpt, double c,
+                            uint32_t tower, uint64_t poly, uint64_t coeff, int64_t *digits_out) {
+    const uint64_t base = 1ULL << base_bits;
+    const double bf = (double)base;
+    const double sigma = c / (bf + 1.0);
+    const double kf = (double)dpt;
+    const uint32_t last = dpt - 1;
+
+    int64_t qd[DMAX], vd[DMAX], z[DMAX];
+    double cv[DMAX], a[DMAX], zf[DMAX];
+    {
+        uint64_t qq = q, vv = value;
+        for (uint32_t i = 0; i < dpt; i++) {
+            qd[i] = (int64_t)(qq & (base - 1));
+            vd[i] = (int64_t)(vv & (base - 1));
+            qq >>= base_bits;
+            vv >>= base_bits;
+        }
+    }
+    cv[0] = (double)qd[0] / bf;
+    for (uint32_t i = 1; i < dpt; i++) cv[i] = (cv[i - 1] + (double)qd[i]) / bf;
+
+    ChaChaStream g;
+    g.open(seed, (uint64_t)tower + 1, poly + 1, coeff + 1, kDomGadget);
+    for (uint32_t i = 0; i < dpt; i++) zf[i] = sigma * g.normal();
+
+    // perturbation p = L-factor of the covariance times zf, folded into the running target a
+    double prev = 0.0;
+    for (uint32_t t = 0; t < dpt; t++) {
+        const double lt = t == 0 ? sqrt(bf * (1.0 + 1.0 / kf) + 1.0) : sqrt(bf * (1.0 + 1.0 / (kf - (double)t)));
+        double p;
+        if (t < last) {
+            const double hn = sqrt(bf * (1.0 - 1.0 / (kf - (double)t)));  // h[t+1]
+            p = lt * zf[t] + hn * zf[t + 1];
+        } else {
+            const double hl = t == 0 ? 0.0 : sqrt(bf * (1.0 - 1.0 / (kf - (double)(t - 1))));  // h[last]
+            p = hl * zf[t];
+        }
+        a[t] = t == 0 ? ((double)vd[0] - p) / bf : (prev + (double)vd[t] - p) / bf;
+        prev = a[t];
+    }
+
+    z[last] = karney_integer(g, -a[last] / cv[last], sigma / cv[last]);
+    for (uint32_t i = 0; i < dpt; i++) a[i] += (double)z[last] * cv[i];
+    for (uint32_t i = 0; i < last; i++) z[i] = karney_integer(g, -a[i], sigma);
+
+    const int64_t sb = (int64_t)base;
+    if (dpt == 1) {
+        digits_out[0] = sb * z[0] + qd[0] * z[0] + vd[0];
+        return;
+    }
+    digits_out[0] = sb * z[0] + qd[0] * z[last] + vd[0];
+    for (uint32_t i = 1; i < last; i++) digits_out[i] = sb * z[i] - z[i - 1] + qd[i] * z[last] + vd[i];
+    digits_out[last] = qd[last] * z[last] - z[last - 1] + vd[last];
+}
+
+// ---- perturbation p1: per-coefficient 2d x 2d conditional Gaussian ----------------------
+// Tables are coefficient-minor ([entry][n]) so that neighbouring threads read neighbouring
+// words (the reference keeps them coefficient-major, MatrixTrapdoor.cu:92-93).
+//   sd  [m][n]    : conditional standard deviation of row t given rows > t
+//   upd [m*m][n]  : upd[t*m + i] = cov(i, t | rows > t) / var(t | rows > t),  i < t
+// `cov` is an [m*m][n] scratch.  centred_abd(which, i, j) returns the centred limb-0
+// coefficient of A (0), B (1) or D (2) at (i, j).
+template <typename LoadABD>
+GP_HD void p1_factor_coeff(LoadABD centred_abd, uint32_t d, size_t n, size_t coeff, double sigma, double s, double dgg_stddev,
+                           double *cov, double *sd, double *upd) {
+    const uint32_t m = 2 * d;
+    const double sigma2 = sigma * sigma;
+    const double s2 = s * s;
+    const double fallback_var = dgg_stddev * dgg_stddev;
+    const double eps = 1e-9;
+#define GP_COV(i, j) cov[((size_t)(i) * m + (j)) * n + coeff]
+#define GP_UPD(t, i) upd[((size_t)(t) * m + (i)) * n + coeff]
+    for (uint32_t i = 0; i < d; i++)
+        for (uint32_t j = 0; j < d; j++) {
+            const double a_ij = (double)centred_abd(0, i, j);
+            const double d_ij = (double)centred_abd(2, i, j);
+            const double b_ij = (double)centred_abd(1, i, j);
+            const double b_ji = (double)centred_abd(1, j, i);
+            GP_COV(i, j) = -sigma2 * a_ij + (i == j ? s2 : 0.0);
+            GP_COV(i + d, j + d) = -sigma2 * d_ij + (i == j ? s2 : 0.0);
+            GP_COV(i, j + d) = -sigma2 * b_ij;
+            GP_COV(i + d, j) = -sigma2 * b_ji;
+        }
+    for (int t = (int)m - 1; t >= 0; --t) {
+        double var = GP_COV(t, t);
+        if (!(var > eps)) var = fallback_var;
+        sd[(size_t)t * n + coeff] = sqrt(var);
+        for (int i = 0; i < t; i++) GP_UPD(t, i) = GP_COV(i, t) / var;
+        // Schur complement of row/column t
+        for (int i = 0; i < t; i++) {
+            const double ci = GP_UPD(t, i);
+            for (int j = 0; j <= i; j++) {
+                const double cj = GP_UPD(t, j) * var;
+                const double v = GP_COV(i, j) - ci * cj;
+                GP_COV(i, j) = v;
+                GP_COV(j, i) = v;
+            }
+        }
+    }
+#undef GP_COV
+}
+
+// one (column, coefficient) of the perturbation: rows sampled from the last to the first,
+// each conditioned on the ones already drawn.  `mean` (m doubles) and `zs` (m integers) are
+// caller-provided scratch with element stride `st` (1 for thread-local arrays).
+template <typename LoadTp2>
+GP_HD void p1_sample_column(LoadTp2 centred_tp2, const Seed256 &seed, uint32_t m, size_t n, size_t col, size_t coeff,
+                            double c_scale, const double *sd, const double *upd, double *mean, int64_t *zs, size_t st) {
+    ChaChaStream g;
+    g.open(seed, (uint64_t)col + 1, (uint64_t)coeff + 1, 0, kDomPerturb);
+    for (uint32_t r = 0; r < m; r++) mean[r * st] = c_scale * (double)centred_tp2(r);
+    for (int t = (int)m - 1; t >= 0; --t) {
+        const double mu = mean[(size_t)t * st];
+        const int64_t zt = karney_integer(g, mu, sd[(size_t)t * n + coeff]);
+        zs[(size_t)t * st] = zt;
+        if (t == 0) break;
+        const double delta = (double)zt - mu;
+        for (int i = 0; i < t; i++) mean[(size_t)i * st] += GP_UPD(t, i) * delta;
+    }
+#undef GP_UPD
+}
+
+// ---- kernels ----------------------------------------------------------------------------
+template <typename T> GP_HD T small_to_residue(int64_t z, const LimbConst<T> &c) {
+    if (z >= 0) return red64<T>((uint64_t)z, c);
+    const T r = red64<T>((uint64_t)(-(z + 1)) + 1, c);
+    return r == 0 ? (T)0 : (T)(c.q - r);
+}
+
+struct SampleGeom {
+    size_t polys;       // rows * local columns
+    size_t local_cols;  // columns of `out`
+    size_t full_cols;   // columns of the matrix `out` is a slice of (stream indexing)
+    size_t col_offset;
+    uint32_t n;
+    uint32_t limbs;
+};
+
+#ifdef __CUDACC__
+// Gauss / bit / ternary: one thread per (poly, coeff) draws the integer once and writes every
+// limb (the reference re-runs the sampler per limb, MatrixSampling.cu:260-293).
+template <typename T>
+__global__ void __launch_bounds__(256) sample_small_kernel(T *__restrict__ dst, SampleGeom g, int dist, double sigma, Seed256 seed,
+                                                           const LimbConst<T> *__restrict__ lc) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= g.polys * g.n) return;
+    const size_t poly = idx / g.n, coeff = idx - poly * g.n;
+    const size_t row = poly / g.local_cols, col = poly - row * g.local_cols;
+    const int64_t z = draw_small_integer(seed, dist, sigma, row * g.full_cols + g.col_offset + col, coeff);
+    T *p = dst + poly * g.limbs * (size_t)g.n + coeff;
+    for (uint32_t l = 0; l < g.limbs; l++) p[(size_t)l * g.n] = small_to_residue<T>(z, lc[l]);
+}
+
+// uniform: one stream per stored word, storage order
+template <typename T>
+__global__ void __launch_bounds__(256) sample_uniform_kernel(T *__restrict__ dst, SampleGeom g, Seed256 seed,
+                                                             const LimbConst<T> *__restrict__ lc) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= g.polys * g.limbs * g.n) return;
+    const size_t pl = idx / g.n, coeff = idx - pl * g.n;
+    const size_t poly = pl / g.limbs;
+    const uint32_t limb = (uint32_t)(pl - poly * g.limbs);
+    const size_t row = poly / g.local_cols, col = poly - row * g.local_cols;
+    dst[idx] = (T)draw_uniform_residue(seed, row * g.full_cols + g.col_offset + col, coeff, limb, (uint64_t)lc[limb].q);
+}
+
+// G-lattice sampling fused with the scatter: thread (src poly, tower, coeff) reads one residue and
+// writes dpt digit coefficients into all limbs of output rows row*ell + tower*dpt + digit
+// (replaces sample kernel + int64 staging + scatter kernel per tower, MatrixTrapdoor.cu:701-897).
+template <typename T, int DMAX>
+__global__ void __launch_bounds__(128) gauss_samp_gq_kernel(const T *__restrict__ src, T *__restrict__ out, size_t src_polys,
+                                                            size_t src_cols, uint32_t n, uint32_t limbs, uint32_t base_bits,
+                                                            uint32_t dpt, double c, Seed256 seed,
+                                                            const LimbConst<T> *__restrict__ lc) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= src_polys * limbs * n) return;
+    const size_t pl = idx / n, coeff = idx - pl * n;
+    const size_t poly = pl / limbs;
+    const uint32_t tower = (uint32_t)(pl - poly * limbs);
+    int64_t digits[DMAX];
+    gq_sample_digits<DMAX>(seed, (uint64_t)src[idx], (uint64_t)lc[tower].q, base_bits, dpt, c, tower, poly, coeff, digits);
+    const size_t row = poly / src_cols, col = poly - row * src_cols;
+    const size_t ell = (size_t)dpt * limbs;
+    for (uint32_t dg = 0; dg < dpt; dg++) {
+        const size_t out_poly = (row * ell + (size_t)tower * dpt + dg) * src_cols + col;
+        T *p = out + out_poly * limbs * (size_t)n + coeff;
+        for (uint32_t l = 0; l < limbs; l++) p[(size_t)l * n] = small_to_residue<T>(digits[dg], lc[l]);
+    }
+}
+
+// covariance factorisation: one thread per coefficient (limb 0 of A, B, D in coefficient form)
+template <typename T>
+__global__ void __launch_bounds__(128) p1_factor_kernel(const T *__restrict__ a, const T *__restrict__ b, const T *__restrict__ dm,
+                                                        uint32_t d, uint32_t n, uint32_t limbs, uint64_t q0, double sigma, double s,
+                                                        double dgg_stddev, double *cov, double *sd, double *upd) {
+    const size_t coeff = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (coeff >= n) return;
+    auto load = [&](int which, uint32_t i, uint32_t j) -> int64_t {
+        const T *base = which == 0 ? a : (which == 1 ? b : dm);
+        return centred((uint64_t)base[((size_t)i * d + j) * limbs * (size_t)n + coeff], q0);
+    };
+    p1_factor_coeff(load, d, (size_t)n, coeff, sigma, s, dgg_stddev, cov, sd, upd);
+}
+
+// perturbation sampling fused with the reduction into every limb: thread (column, coeff).
+// MLOC > 0: scratch in registers/local memory; MLOC == 0: [m][cols*n] global scratch.
+template <typename T, int MLOC>
+__global__ void __launch_bounds__(128) p1_sample_kernel(const T *__restrict__ tp2, T *__restrict__ out, uint32_t m, size_t cols,
+                                                        uint32_t n, uint32_t limbs, uint64_t q0, double c_scale, Seed256 seed,
+                                                        const double *__restrict__ sd, const double *__restrict__ upd,
+                                                        double *mean_ws, int64_t *z_ws, const LimbConst<T> *__restrict__ lc) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t total = cols * n;
+    if (idx >= total) return;
+    const size_t col = idx / n, coeff = idx - col * n;
+    auto load = [&](uint32_t r) -> int64_t {
+        return centred((uint64_t)tp2[((size_t)r * cols + col) * limbs * (size_t)n + coeff], q0);
+    };
+    double mean_loc[MLOC > 0 ? MLOC : 1];
+    int64_t z_loc[MLOC > 0 ? MLOC : 1];
+    double *mean = MLOC > 0 ? mean_loc : mean_ws + idx;
+    int64_t *zs = MLOC > 0 ? z_loc : z_ws + idx;
+    const size_t st = MLOC > 0 ? 1 : total;
+    p1_sample_column(load, seed, m, (size_t)n, col, coeff, c_scale, sd, upd, mean, zs, st);
+    for (uint32_t r = 0; r < m; r++) {
+        const int64_t z = zs[(size_t)r * st];
+        T *p = out + ((size_t)r * cols + col) * limbs * (size_t)n + coeff;
+        for (uint32_t l = 0; l < limbs; l++) p[(size_t)l * n] = small_to_residue<T>(z, lc[l]);
+    }
+}
+#endif  // __CUDACC__
+
+}  // namespace gp

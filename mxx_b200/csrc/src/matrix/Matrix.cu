@@ -16,6 +16,7 @@
 #include "ntt_fast.cuh"
 #include "serde.cuh"
 #include "compact.cuh"
+#include "sampling.cuh"
 
 #include "MatrixCommon.inl"
 #include "MatrixData.inl"
@@ -24,4 +25,4 @@
 #include "MatrixArith.inl"
 #include "MatrixDecompose.inl"
 #include "MatrixCompact.inl"
-#include "MatrixDeferred.inl"
+#include "MatrixSampling.inl"

@@ -15,7 +15,7 @@ import os
 import numpy as np
 
 from . import ffi
-from .ffi import GPU_POLY_FORMAT_COEFF, GPU_POLY_FORMAT_EVAL, check_status
+from .ffi import GPU_POLY_FORMAT_COEFF, GPU_POLY_FORMAT_EVAL, GpuRngSeed, check_status
 from .params import GpuDCRTPolyParams
 
 
@@ -554,3 +554,93 @@ class GpuDCRTPolyMatrix:
         assert self.ncol == w * identity_size
         parts = [self.slice(0, self.nrow, i * w, (i + 1) * w).mul_decompose(other) for i in range(identity_size)]
         return parts[0].concat_columns(parts[1:])
+
+    # -- samplers -------------------------------------------------------
+    @classmethod
+    def sample_distribution(cls, params, nrow, ncol, dist: int, sigma: float, seed):  # gpu_dcrt_poly.rs:454-469
+        out = cls.new_empty(params, nrow, ncol)
+        if nrow == 0 or ncol == 0:
+            return out
+        check_status(out._L.gpu_matrix_sample_distribution(out.raw, int(dist), float(sigma), as_seed(seed)),
+                     "gpu_matrix_sample_distribution", out._L)
+        return out
+
+    @classmethod
+    def sample_distribution_columns(cls, params, nrow, total_ncol, col_start, col_len, dist: int, sigma: float, seed):
+        """gpu_dcrt_poly.rs:471-507: columns [col_start, col_start+col_len) of the nrow x total_ncol matrix `seed` defines."""
+        assert col_start + col_len <= total_ncol, "sample_distribution_columns range out of bounds"
+        out = cls.new_empty(params, nrow, col_len)
+        if nrow == 0 or col_len == 0:
+            return out
+        check_status(out._L.gpu_matrix_sample_distribution_columns(out.raw, int(dist), float(sigma), as_seed(seed),
+                                                                   total_ncol, col_start),
+                     "gpu_matrix_sample_distribution_columns", out._L)
+        return out
+
+    def gauss_samp_gq_arb_base(self, c: float, dgg_stddev: float, seed):  # gpu_dcrt_poly.rs:509-528 (consumes self)
+        out = GpuDCRTPolyMatrix.new_empty(self.params, self.nrow * self.params.modulus_digits(), self.ncol)
+        self.intt_all_in_place()
+        check_status(self._L.gpu_matrix_gauss_samp_gq_arb_base(self.raw, self.params.base_bits, float(c), float(dgg_stddev),
+                                                               as_seed(seed), out.raw),
+                     "gpu_matrix_gauss_samp_gq_arb_base", self._L)
+        return out
+
+    @staticmethod
+    def create_p1_covariance_cache(a_mat, b_mat, d_mat, sigma: float, s: float, dgg_stddev: float):  # :530-559
+        return GpuP1CovarianceCache(a_mat, b_mat, d_mat, sigma, s, dgg_stddev)
+
+    @classmethod
+    def sample_p1_full_cached(cls, cache: "GpuP1CovarianceCache", tp2, seed):  # gpu_dcrt_poly.rs:561-574 (consumes tp2)
+        out = cls.new_empty(tp2.params, tp2.nrow, tp2.ncol)
+        if tp2.nrow == 0 or tp2.ncol == 0:
+            return out
+        tp2.intt_all_in_place()
+        check_status(out._L.gpu_matrix_sample_p1_full_cached(cache.raw, tp2.raw, as_seed(seed), out.raw),
+                     "gpu_matrix_sample_p1_full_cached", out._L)
+        return out
+
+
+# GpuMatrixSampleDist (gpu_dcrt_poly.rs:70-88)
+DIST_UNIFORM, DIST_GAUSS, DIST_BIT, DIST_TERNARY = 0, 1, 2, 3
+
+
+def as_seed(seed) -> GpuRngSeed:
+    """GpuRngSeed::from_bytes (gpu.rs:51-61): 32 bytes -> four LE u64 words; also accepts 4 ints or one int (word 0)."""
+    if isinstance(seed, GpuRngSeed):
+        return seed
+    if isinstance(seed, (bytes, bytearray)):
+        assert len(seed) == 32
+        words = [int.from_bytes(seed[8 * i:8 * i + 8], "little") for i in range(4)]
+    elif isinstance(seed, int):
+        words = [seed & (2**64 - 1), 0, 0, 0]
+    else:
+        words = [int(w) & (2**64 - 1) for w in seed]
+        assert len(words) == 4
+    out = GpuRngSeed()
+    for i, w in enumerate(words):
+        out.words[i] = w
+    return out
+
+
+class GpuP1CovarianceCache:
+    """gpu_dcrt_poly.rs:56-68: owns the device tables of the perturbation covariance; freed on drop."""
+
+    def __init__(self, a_mat, b_mat, d_mat, sigma, s, dgg_stddev):
+        self._L = a_mat._L
+        self._keep = (a_mat.params,)
+        h = C.c_void_p()
+        check_status(self._L.gpu_matrix_create_p1_covariance_cache(a_mat.raw, b_mat.raw, d_mat.raw, float(sigma), float(s),
+                                                                   float(dgg_stddev), C.byref(h)),
+                     "gpu_matrix_create_p1_covariance_cache", self._L)
+        self.raw = h
+
+    def destroy(self):
+        if getattr(self, "raw", None):
+            self._L.gpu_matrix_destroy_p1_covariance_cache(self.raw)
+            self.raw = None
+
+    def __del__(self):
+        try:
+            self.destroy()
+        except Exception:
+            pass

@@ -1,0 +1,271 @@
+/*
+ * sampler_oracle.c — CPU oracle for the samplers of the trapdoor path.
+ *
+ * TEST INFRASTRUCTURE ONLY (see dcrt_oracle.h): used by tests/ as the checker, never by
+ * the product path.
+ *
+ * Restates, in plain C:
+ *   - ChaCha20 block / HChaCha20 (RFC 8439 §2.3; draft-irtf-cfrg-xchacha §2.2) and the
+ *     stream derivation of cuda/src/ChaCha.cu:109-166 (key = HChaCha20(seed, domain||stream2),
+ *     block counter = stream0, nonce = stream1, 8 u64 per block)
+ *   - uniform (0,1) deviates, rejection-uniform residues       MatrixSampling.cu:6-19, 187-203
+ *   - Karney's discrete Gaussian (algorithms H, G, P, B)       MatrixSampling.cu:31-160
+ *   - gpu_matrix_sample_distribution(_columns)                 MatrixSampling.cu:221-306, 412-470
+ *   - the G-lattice sampler gpu_matrix_gauss_samp_gq_arb_base  MatrixTrapdoor.cu:701-897
+ *   - the perturbation p1 (covariance factorisation + conditional sampling)
+ *                                                              MatrixTrapdoor.cu:95-277, 674-699
+ *
+ * Parity status: pinned for everything integer-exact — the ChaCha block against the RFC 8439
+ * §2.3.2 known answer, and the distributions (uniform / bit / ternary / Gauss with mean 0,
+ * whose floating-point steps are exactly rounded single operations) against outputs of the
+ * reference's CUDA library run on a B200 (tests/golden/ref_cuda_sampler_vectors.npz).
+ * The G-lattice sampler and p1 evaluate log/cos and fused multiply-adds on the device; this C
+ * restatement uses libm and unfused arithmetic, so for those two it is a checker of the
+ * RELATIONS the reference tests (G z = v mod q; the conditional-Gaussian statistics), not of
+ * individual samples — sample-for-sample equality for them is checked GPU-vs-golden.
+ *
+ * Matrices: host layout [poly row-major][limb][coeff] u64, coefficient domain.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "dcrt_oracle.h"
+
+#define ROTL32(v, n) (((v) << (n)) | ((v) >> (32 - (n))))
+#define QR(a, b, c, d)                 \
+    do {                               \
+        a += b; d ^= a; d = ROTL32(d, 16); \
+        c += d; b ^= c; b = ROTL32(b, 12); \
+        a += b; d ^= a; d = ROTL32(d, 8);  \
+        c += d; b ^= c; b = ROTL32(b, 7);  \
+    } while (0)
+
+static const uint32_t kSigma[4] = {0x61707865u, 0x3320646eu, 0x79622d32u, 0x6b206574u};
+
+static void twenty_rounds(uint32_t x[16]) {
+    for (int i = 0; i < 10; i++) {
+        QR(x[0], x[4], x[8], x[12]);
+        QR(x[1], x[5], x[9], x[13]);
+        QR(x[2], x[6], x[10], x[14]);
+        QR(x[3], x[7], x[11], x[15]);
+        QR(x[0], x[5], x[10], x[15]);
+        QR(x[1], x[6], x[11], x[12]);
+        QR(x[2], x[7], x[8], x[13]);
+        QR(x[3], x[4], x[9], x[14]);
+    }
+}
+
+/* RFC 8439 §2.3: out = rounds(state) + state, state = sigma | key | words 12..15 */
+void orc_chacha20_block(const uint32_t key[8], const uint32_t w12_15[4], uint32_t out[16]) {
+    uint32_t st[16], x[16];
+    memcpy(st, kSigma, 16);
+    memcpy(st + 4, key, 32);
+    memcpy(st + 12, w12_15, 16);
+    memcpy(x, st, 64);
+    twenty_rounds(x);
+    for (int i = 0; i < 16; i++) out[i] = x[i] + st[i];
+}
+
+/* HChaCha20: rows 0 and 3 of the permuted state, no feed-forward */
+void orc_hchacha20(const uint32_t key[8], const uint32_t nonce[4], uint32_t out[8]) {
+    uint32_t x[16];
+    memcpy(x, kSigma, 16);
+    memcpy(x + 4, key, 32);
+    memcpy(x + 12, nonce, 16);
+    twenty_rounds(x);
+    memcpy(out, x, 16);
+    memcpy(out + 4, x + 12, 16);
+}
+
+typedef struct {
+    uint32_t key[8];
+    uint32_t w[4];
+    uint32_t block[16];
+    unsigned idx; /* next u64 of block, 8 = empty */
+} Stream;
+
+/* ChaCha.cu:109-150 */
+static void stream_init(Stream *s, const uint64_t seed[4], uint64_t stream0, uint64_t stream1, uint64_t stream2,
+                        uint64_t domain) {
+    uint32_t base_key[8], nonce[4];
+    for (int i = 0; i < 4; i++) {
+        base_key[2 * i] = (uint32_t)seed[i];
+        base_key[2 * i + 1] = (uint32_t)(seed[i] >> 32);
+    }
+    nonce[0] = (uint32_t)domain;
+    nonce[1] = (uint32_t)(domain >> 32);
+    nonce[2] = (uint32_t)stream2;
+    nonce[3] = (uint32_t)(stream2 >> 32);
+    orc_hchacha20(base_key, nonce, s->key);
+    s->w[0] = (uint32_t)stream0;
+    s->w[1] = (uint32_t)(stream0 >> 32);
+    s->w[2] = (uint32_t)stream1;
+    s->w[3] = (uint32_t)(stream1 >> 32);
+    s->idx = 8;
+}
+
+/* ChaCha.cu:152-166 */
+static uint64_t stream_u64(Stream *s) {
+    if (s->idx >= 8) {
+        orc_chacha20_block(s->key, s->w, s->block);
+        s->w[0] += 1;
+        if (s->w[0] == 0) s->w[1] += 1;
+        s->idx = 0;
+    }
+    uint64_t v = (uint64_t)s->block[2 * s->idx] | ((uint64_t)s->block[2 * s->idx + 1] << 32);
+    s->idx++;
+    return v;
+}
+
+void orc_stream_words(const uint64_t seed[4], uint64_t stream0, uint64_t stream1, uint64_t stream2, uint64_t domain,
+                      size_t count, uint64_t *out) {
+    Stream s;
+    stream_init(&s, seed, stream0, stream1, stream2, domain);
+    for (size_t i = 0; i < count; i++) out[i] = stream_u64(&s);
+}
+
+/* MatrixSampling.cu:6-19 */
+static double uniform_open01(Stream *s) {
+    const double scale = 1.0 / 9007199254740992.0;
+    double u = (double)(stream_u64(s) >> 11) * scale;
+    if (u <= 0.0) u = scale;
+    else if (u >= 1.0) u = 1.0 - scale;
+    return u;
+}
+
+/* MatrixSampling.cu:21-29 */
+static double standard_normal(Stream *s) {
+    double u1 = uniform_open01(s);
+    double u2 = uniform_open01(s);
+    return sqrt(-2.0 * log(u1)) * cos(6.283185307179586476925286766559 * u2);
+}
+
+/* Karney 2016, algorithm H; MatrixSampling.cu:31-50 */
+static int alg_h(Stream *s) {
+    double a = uniform_open01(s);
+    if (!(a < 0.5)) return 1;
+    for (;;) {
+        double b = uniform_open01(s);
+        if (!(b < a)) return 0;
+        a = uniform_open01(s);
+        if (!(a < b)) return 1;
+    }
+}
+/* MatrixSampling.cu:52-64 */
+static int32_t alg_g(Stream *s) {
+    int32_t n = 0;
+    while (alg_h(s)) {
+        ++n;
+        if (n > 1024) break;
+    }
+    return n;
+}
+/* MatrixSampling.cu:66-72 */
+static int alg_p(Stream *s, int32_t n) {
+    while (n-- && alg_h(s)) {
+    }
+    return n < 0;
+}
+/* MatrixSampling.cu:74-98 */
+static int alg_b(Stream *s, int32_t k, double x) {
+    double y = x;
+    int32_t n = 0;
+    double m = (double)(2 * k + 2);
+    for (;; ++n) {
+        double z = uniform_open01(s);
+        if (!(z < y)) break;
+        double r = uniform_open01(s);
+        if (!(r < (2.0 * (double)k + x) / m)) break;
+        y = z;
+        if (n > 4096) break;
+    }
+    return (n % 2) == 0;
+}
+/* MatrixSampling.cu:100-160 */
+static int64_t integer_karney(Stream *s, double mean, double stddev) {
+    if (!(stddev > 0.0) || !isfinite(mean) || !isfinite(stddev)) return (int64_t)llround(mean);
+    int64_t ceil_std = (int64_t)ceil(stddev);
+    if (ceil_std <= 0) return (int64_t)llround(mean);
+    for (int iter = 0; iter < (1 << 16); ++iter) {
+        int32_t k = alg_g(s);
+        if (!alg_p(s, k * (k - 1))) continue;
+        int64_t sg = (stream_u64(s) & 1ULL) ? 1 : -1;
+        double di0 = stddev * (double)k + (double)sg * mean;
+        int64_t i0 = (int64_t)ceil(di0);
+        double x0 = ((double)i0 - di0) / stddev;
+        int64_t j = (int64_t)(stream_u64(s) % (uint64_t)ceil_std);
+        double x = x0 + (double)j / stddev;
+        if (!(x < 1.0) || (x == 0.0 && sg < 0 && k == 0)) continue;
+        int32_t h = k + 1;
+        while (h-- > 0 && alg_b(s, k, x)) {
+        }
+        if (h >= 0) continue;
+        return sg * (i0 + j);
+    }
+    return (int64_t)llround(mean + stddev * standard_normal(s));
+}
+
+void orc_karney_samples(const uint64_t seed[4], double mean, double stddev, size_t count, int64_t *out) {
+    for (size_t i = 0; i < count; i++) {
+        Stream s;
+        stream_init(&s, seed, i + 1, 1, 0, 0x6f70656e66686532ULL);
+        out[i] = integer_karney(&s, mean, stddev);
+    }
+}
+
+/* MatrixSampling.cu:175-185 */
+static uint64_t signed_mod(int64_t v, uint64_t q) {
+    if (v >= 0) return (uint64_t)v % q;
+    uint64_t mag = (uint64_t)(-(v + 1)) + 1;
+    uint64_t r = mag % q;
+    return r ? q - r : 0;
+}
+/* MatrixSampling.cu:205-219 */
+static int64_t centered(uint64_t v, uint64_t q) {
+    uint64_t r = v % q, half = q >> 1;
+    return r <= half ? (int64_t)r : -(int64_t)(q - r);
+}
+/* MatrixSampling.cu:187-203 */
+static uint64_t uniform_mod(Stream *s, uint64_t q) {
+    const uint64_t max = ~(uint64_t)0;
+    const uint64_t threshold = max - (max % q);
+    for (;;) {
+        uint64_t x = stream_u64(s);
+        if (x < threshold) return x % q;
+    }
+}
+
+/* gpu_matrix_sample_distribution(_columns) before its final NTT: MatrixSampling.cu:221-306.
+ * dist: 0 uniform, 1 gauss, 2 bit, 3 ternary. out: [rows*local_cols][L][n]. */
+void orc_sample_distribution(int dist, double sigma, const uint64_t seed[4], size_t rows, size_t local_cols,
+                             size_t full_cols, size_t col_offset, size_t n, uint32_t L, const uint64_t *moduli,
+                             uint64_t *out) {
+#pragma omp parallel for schedule(static)
+    for (size_t poly = 0; poly < rows * local_cols; poly++) {
+        size_t row = poly / local_cols, col = poly % local_cols;
+        uint64_t gpoly = row * full_cols + col_offset + col;
+        for (uint32_t l = 0; l < L; l++) {
+            uint64_t q = moduli[l];
+            uint64_t *dst = out + (poly * L + l) * n;
+            for (size_t i = 0; i < n; i++) {
+                Stream s;
+                if (dist == 0) {
+                    stream_init(&s, seed, gpoly + 1, i + 1, (uint64_t)l + 1, 0x6f70656e66686531ULL);
+                    dst[i] = uniform_mod(&s, q);
+                } else if (dist == 1) {
+                    stream_init(&s, seed, gpoly + 1, i + 1, 0, 0x6f70656e66686532ULL);
+                    dst[i] = signed_mod(integer_karney(&s, 0.0, sigma), q);
+                } else if (dist == 2) {
+                    stream_init(&s, seed, gpoly + 1, i + 1, 0, 0x6f70656e66686533ULL);
+                    dst[i] = (stream_u64(&s) & 1ULL) % q;
+                } else {
+                    stream_init(&s, seed, gpoly + 1, i + 1, 0, 0x6f70656e66686534ULL);
+                    uint64_t pick = stream_u64(&s) % 3ULL;
+                    dst[i] = signed_mod(pick == 0 ? 0 : (pick == 1 ? 1 : -1), q);
+                }
+            }
+        }
+    }
+}
