@@ -20,6 +20,7 @@
 #include "host_tables.hpp"
 #include "ntt.cuh"
 #include "ntt_fast.cuh"
+#include "sampling.cuh"
 
 namespace {
 using namespace gp;
@@ -255,9 +256,119 @@ bool wide_for(const uint64_t *moduli, uint32_t limbs) {
     for (uint32_t i = 0; i < limbs; i++) qmax = moduli[i] > qmax ? moduli[i] : qmax;
     return host::needs_wide(qmax);
 }
+
+// ---- samplers (sampling.cuh): the same per-element functions the kernels call, looped over
+// the kernels' index space.  Coefficient-domain u64 words in host layout.
+template <typename T> int do_sample_distribution(int logn, uint32_t limbs, const uint64_t *moduli, int dist, double sigma,
+                                                 const uint64_t *seed, size_t rows, size_t local_cols, size_t full_cols,
+                                                 size_t col_offset, uint64_t *out) {
+    Emu<T> e(logn, limbs, moduli);
+    const size_t n = (size_t)1 << logn;
+    Seed256 sd;
+    for (int i = 0; i < 4; i++) sd.w[i] = seed[i];
+    for (size_t poly = 0; poly < rows * local_cols; poly++) {
+        const size_t row = poly / local_cols, col = poly - row * local_cols;
+        const uint64_t gp = row * full_cols + col_offset + col;
+        for (size_t c = 0; c < n; c++) {
+            if (dist == kDistUniform) {
+                for (uint32_t l = 0; l < limbs; l++)
+                    out[(poly * limbs + l) * n + c] = draw_uniform_residue(sd, gp, c, l, (uint64_t)e.tab.limb[l].q);
+            } else {
+                const int64_t z = draw_small_integer(sd, dist, sigma, gp, c);
+                for (uint32_t l = 0; l < limbs; l++) out[(poly * limbs + l) * n + c] = small_to_residue<T>(z, e.tab.limb[l]);
+            }
+        }
+    }
+    return 0;
+}
+template <typename T> int do_gauss_samp(int logn, uint32_t limbs, const uint64_t *moduli, const uint64_t *src, size_t rows,
+                                        size_t cols, uint32_t base_bits, uint32_t dpt, double c, const uint64_t *seed,
+                                        uint64_t *out) {
+    Emu<T> e(logn, limbs, moduli);
+    const size_t n = (size_t)1 << logn, ell = (size_t)dpt * limbs;
+    Seed256 sd;
+    for (int i = 0; i < 4; i++) sd.w[i] = seed[i];
+    for (size_t poly = 0; poly < rows * cols; poly++) {
+        const size_t row = poly / cols, col = poly - row * cols;
+        for (uint32_t tower = 0; tower < limbs; tower++)
+            for (size_t ci = 0; ci < n; ci++) {
+                int64_t digits[kMaxGaussDigits];
+                const uint64_t v = src[(poly * limbs + tower) * n + ci];
+                if (dpt <= 8) gq_sample_digits<8>(sd, v, (uint64_t)e.tab.limb[tower].q, base_bits, dpt, c, tower, poly, ci, digits);
+                else gq_sample_digits<kMaxGaussDigits>(sd, v, (uint64_t)e.tab.limb[tower].q, base_bits, dpt, c, tower, poly, ci, digits);
+                for (uint32_t dg = 0; dg < dpt; dg++) {
+                    const size_t op = (row * ell + (size_t)tower * dpt + dg) * cols + col;
+                    for (uint32_t l = 0; l < limbs; l++) out[(op * limbs + l) * n + ci] = small_to_residue<T>(digits[dg], e.tab.limb[l]);
+                }
+            }
+    }
+    return 0;
+}
+template <typename T> int do_sample_p1(int logn, uint32_t limbs, const uint64_t *moduli, const uint64_t *a, const uint64_t *b,
+                                       const uint64_t *dm, const uint64_t *tp2, uint32_t d, size_t cols, double sigma, double s,
+                                       double dgg, const uint64_t *seed, uint64_t *out) {
+    Emu<T> e(logn, limbs, moduli);
+    const size_t n = (size_t)1 << logn;
+    const uint32_t m = 2 * d;
+    const uint64_t q0 = moduli[0];
+    Seed256 sd;
+    for (int i = 0; i < 4; i++) sd.w[i] = seed[i];
+    std::vector<double> cov((size_t)m * m * n), upd((size_t)m * m * n), sdv((size_t)m * n), mean(m);
+    std::vector<int64_t> zs(m);
+    const double c_scale = -(sigma * sigma) / (s * s - sigma * sigma);
+    for (size_t ci = 0; ci < n; ci++) {
+        auto load = [&](int which, uint32_t i, uint32_t j) -> int64_t {
+            const uint64_t *base = which == 0 ? a : (which == 1 ? b : dm);
+            return centred(base[((size_t)i * d + j) * limbs * n + ci], q0);
+        };
+        p1_factor_coeff(load, d, n, ci, sigma, s, dgg, cov.data(), sdv.data(), upd.data());
+    }
+    for (size_t col = 0; col < cols; col++)
+        for (size_t ci = 0; ci < n; ci++) {
+            auto load = [&](uint32_t r) -> int64_t { return centred(tp2[((size_t)r * cols + col) * limbs * n + ci], q0); };
+            p1_sample_column(load, sd, m, n, col, ci, c_scale, sdv.data(), upd.data(), mean.data(), zs.data(), 1);
+            for (uint32_t r = 0; r < m; r++)
+                for (uint32_t l = 0; l < limbs; l++)
+                    out[(((size_t)r * cols + col) * limbs + l) * n + ci] = small_to_residue<T>(zs[r], e.tab.limb[l]);
+        }
+    return 0;
+}
 }  // namespace
 
 extern "C" {
+void emu_stream_words(const uint64_t *seed, uint64_t s0, uint64_t s1, uint64_t s2, uint64_t domain, size_t count, uint64_t *out) {
+    Seed256 sd;
+    for (int i = 0; i < 4; i++) sd.w[i] = seed[i];
+    ChaChaStream g;
+    g.open(sd, s0, s1, s2, domain);
+    for (size_t i = 0; i < count; i++) out[i] = g.next();
+}
+int emu_sample_distribution(int force_wide, int logn, uint32_t limbs, const uint64_t *moduli, int dist, double sigma,
+                            const uint64_t *seed, size_t rows, size_t local_cols, size_t full_cols, size_t col_offset,
+                            uint64_t *out) {
+    try {
+        if (force_wide || wide_for(moduli, limbs))
+            return do_sample_distribution<uint64_t>(logn, limbs, moduli, dist, sigma, seed, rows, local_cols, full_cols, col_offset, out);
+        return do_sample_distribution<uint32_t>(logn, limbs, moduli, dist, sigma, seed, rows, local_cols, full_cols, col_offset, out);
+    } catch (...) { return 1; }
+}
+int emu_gauss_samp(int force_wide, int logn, uint32_t limbs, const uint64_t *moduli, const uint64_t *src, size_t rows, size_t cols,
+                   uint32_t base_bits, uint32_t dpt, double c, const uint64_t *seed, uint64_t *out) {
+    try {
+        if (force_wide || wide_for(moduli, limbs))
+            return do_gauss_samp<uint64_t>(logn, limbs, moduli, src, rows, cols, base_bits, dpt, c, seed, out);
+        return do_gauss_samp<uint32_t>(logn, limbs, moduli, src, rows, cols, base_bits, dpt, c, seed, out);
+    } catch (...) { return 1; }
+}
+int emu_sample_p1(int force_wide, int logn, uint32_t limbs, const uint64_t *moduli, const uint64_t *a, const uint64_t *b,
+                  const uint64_t *dm, const uint64_t *tp2, uint32_t d, size_t cols, double sigma, double s, double dgg,
+                  const uint64_t *seed, uint64_t *out) {
+    try {
+        if (force_wide || wide_for(moduli, limbs))
+            return do_sample_p1<uint64_t>(logn, limbs, moduli, a, b, dm, tp2, d, cols, sigma, s, dgg, seed, out);
+        return do_sample_p1<uint32_t>(logn, limbs, moduli, a, b, dm, tp2, d, cols, sigma, s, dgg, seed, out);
+    } catch (...) { return 1; }
+}
 // force_wide: 0 = the context rule (u32 words when all moduli < 2^30), 1 = u64 words regardless
 int emu_ntt(int force_wide, int logn, uint32_t limbs, const uint64_t *moduli, uint64_t *data, size_t polys, int inverse,
             int logb_cap) {

@@ -112,6 +112,26 @@ void orc_matrix_mul_decompose(const OrcPlan *p, uint64_t *out, const uint64_t *S
                               const uint64_t *other, size_t r, size_t d, size_t c,
                               uint32_t base_bits, int small);
 
+/* ---- samplers of the trapdoor path (sampler_oracle.c) ------------------ */
+void orc_chacha20_block(const uint32_t key[8], const uint32_t w12_15[4], uint32_t out[16]); /* RFC 8439 §2.3 */
+void orc_hchacha20(const uint32_t key[8], const uint32_t nonce[4], uint32_t out[8]);
+/* `count` u64 of the stream cuda/src/ChaCha.cu:109-166 derives from (seed, streams, domain) */
+void orc_stream_words(const uint64_t seed[4], uint64_t stream0, uint64_t stream1, uint64_t stream2, uint64_t domain,
+                      size_t count, uint64_t *out);
+/* sample i drawn from stream (i+1, 1, 0) of the Gauss domain: D_{Z, stddev, mean} */
+void orc_karney_samples(const uint64_t seed[4], double mean, double stddev, size_t count, int64_t *out);
+/* coefficient-domain result of gpu_matrix_sample_distribution(_columns), MatrixSampling.cu:221-306 */
+void orc_sample_distribution(int dist, double sigma, const uint64_t seed[4], size_t rows, size_t local_cols,
+                             size_t full_cols, size_t col_offset, size_t n, uint32_t L, const uint64_t *moduli,
+                             uint64_t *out);
+/* coefficient-domain result of gpu_matrix_gauss_samp_gq_arb_base, MatrixTrapdoor.cu:701-897 */
+void orc_gauss_samp_gq(const uint64_t *src, size_t rows, size_t cols, size_t n, uint32_t L, const uint64_t *moduli,
+                       uint32_t crt_bits, uint32_t base_bits, double c, const uint64_t seed[4], uint64_t *out);
+/* coefficient-domain result of gpu_matrix_sample_p1_full_cached, MatrixTrapdoor.cu:95-277, 674-699 */
+void orc_sample_p1(const uint64_t *a, const uint64_t *b, const uint64_t *dm, const uint64_t *tp2, size_t d, size_t cols,
+                   size_t n, uint32_t L, const uint64_t *moduli, double sigma, double s, double dgg_stddev,
+                   const uint64_t seed[4], uint64_t *out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -19,14 +19,15 @@ _LIB_PATH = os.path.join(_HERE, "liboracle.so")
 
 
 def build(force: bool = False) -> str:
-    src = os.path.join(_HERE, "dcrt_oracle.c")
-    if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < os.path.getmtime(src):
+    srcs = [os.path.join(_HERE, f) for f in ("dcrt_oracle.c", "sampler_oracle.c", "dcrt_oracle.h")]
+    if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-C", _HERE, "liboracle.so"], stdout=subprocess.DEVNULL)
     return _LIB_PATH
 
 
 _lib = None
 u64p = C.POINTER(C.c_uint64)
+u32p = C.POINTER(C.c_uint32)
 
 
 def lib():
@@ -64,6 +65,13 @@ def lib():
             "orc_matrix_decompose": (None, [C.c_void_p, u64p, u64p, C.c_size_t, C.c_size_t, C.c_uint32, C.c_int]),
             "orc_matrix_gadget": (None, [C.c_void_p, u64p, C.c_size_t, C.c_uint32, C.c_int]),
             "orc_matrix_mul_decompose": (None, [C.c_void_p, u64p, u64p, u64p] + [C.c_size_t] * 3 + [C.c_uint32, C.c_int]),
+            "orc_chacha20_block": (None, [u32p, u32p, u32p]),
+            "orc_hchacha20": (None, [u32p, u32p, u32p]),
+            "orc_stream_words": (None, [u64p] + [C.c_uint64] * 4 + [C.c_size_t, u64p]),
+            "orc_karney_samples": (None, [u64p, C.c_double, C.c_double, C.c_size_t, C.POINTER(C.c_int64)]),
+            "orc_sample_distribution": (None, [C.c_int, C.c_double, u64p] + [C.c_size_t] * 5 + [C.c_uint32, u64p, u64p]),
+            "orc_gauss_samp_gq": (None, [u64p] + [C.c_size_t] * 3 + [C.c_uint32, u64p, C.c_uint32, C.c_uint32, C.c_double, u64p, u64p]),
+            "orc_sample_p1": (None, [u64p] * 4 + [C.c_size_t] * 3 + [C.c_uint32, u64p] + [C.c_double] * 3 + [u64p, u64p]),
         }
         for name, (res, args) in sig.items():
             fn = getattr(L, name)
@@ -84,6 +92,39 @@ def prime_chain(n: int, bits: int, depth: int) -> list[int]:
     if k != depth:
         raise ValueError(f"only {k} of {depth} primes below 2^{bits} with p = 1 mod {2 * n}")
     return [int(x) for x in out]
+
+
+def seed_words(seed) -> np.ndarray:
+    """GpuRngSeed words: 4 ints, 32 LE bytes, or one int (word 0)."""
+    if isinstance(seed, (bytes, bytearray)):
+        seed = [int.from_bytes(seed[8 * i:8 * i + 8], "little") for i in range(4)]
+    elif isinstance(seed, int):
+        seed = [seed, 0, 0, 0]
+    return np.array([int(w) & (2**64 - 1) for w in seed], dtype=np.uint64)
+
+
+def chacha20_block(key_words, w12_15) -> np.ndarray:
+    k, w, out = np.array(key_words, dtype=np.uint32), np.array(w12_15, dtype=np.uint32), np.zeros(16, dtype=np.uint32)
+    lib().orc_chacha20_block(k.ctypes.data_as(u32p), w.ctypes.data_as(u32p), out.ctypes.data_as(u32p))
+    return out
+
+
+def hchacha20(key_words, nonce_words) -> np.ndarray:
+    k, w, out = np.array(key_words, dtype=np.uint32), np.array(nonce_words, dtype=np.uint32), np.zeros(8, dtype=np.uint32)
+    lib().orc_hchacha20(k.ctypes.data_as(u32p), w.ctypes.data_as(u32p), out.ctypes.data_as(u32p))
+    return out
+
+
+def stream_words(seed, stream0, stream1, stream2, domain, count) -> np.ndarray:
+    out = np.zeros(count, dtype=np.uint64)
+    lib().orc_stream_words(_p(seed_words(seed)), stream0, stream1, stream2, domain, count, _p(out))
+    return out
+
+
+def karney_samples(seed, mean, stddev, count) -> np.ndarray:
+    out = np.zeros(count, dtype=np.int64)
+    lib().orc_karney_samples(_p(seed_words(seed)), float(mean), float(stddev), count, out.ctypes.data_as(C.POINTER(C.c_int64)))
+    return out
 
 
 class Plan:
@@ -120,6 +161,30 @@ class Plan:
         m = np.ascontiguousarray(m, dtype=np.uint64)
         assert m.ndim == 4 and m.shape[2] == self.L and m.shape[3] == self.n, m.shape
         return m
+
+    # -- samplers (sampler_oracle.c), all coefficient domain ----------------
+    def sample_distribution(self, rows, cols, dist, sigma, seed, full_cols=None, col_offset=0) -> np.ndarray:
+        out = np.empty((rows, cols, self.L, self.n), dtype=np.uint64)
+        lib().orc_sample_distribution(dist, float(sigma), _p(seed_words(seed)), rows, cols, cols if full_cols is None else full_cols,
+                                      col_offset, self.n, self.L, _p(self._mod), _p(out))
+        return out
+
+    def gauss_samp_gq(self, src_coeff: np.ndarray, base_bits: int, c: float, seed) -> np.ndarray:
+        src = self._chk(src_coeff)
+        rows, cols = src.shape[:2]
+        out = np.empty((rows * self.ell(base_bits), cols, self.L, self.n), dtype=np.uint64)
+        lib().orc_gauss_samp_gq(_p(src), rows, cols, self.n, self.L, _p(self._mod), self.crt_bits, base_bits, float(c),
+                                _p(seed_words(seed)), _p(out))
+        return out
+
+    def sample_p1(self, a, b, dm, tp2, sigma, s, dgg_stddev, seed) -> np.ndarray:
+        a, b, dm, tp2 = (self._chk(x) for x in (a, b, dm, tp2))
+        d, cols = a.shape[0], tp2.shape[1]
+        assert tp2.shape[0] == 2 * d
+        out = np.empty_like(tp2)
+        lib().orc_sample_p1(_p(a), _p(b), _p(dm), _p(tp2), d, cols, self.n, self.L, _p(self._mod), float(sigma), float(s),
+                            float(dgg_stddev), _p(seed_words(seed)), _p(out))
+        return out
 
     # -- transforms ------------------------------------------------------
     def ntt(self, m: np.ndarray) -> np.ndarray:

@@ -269,3 +269,123 @@ void orc_sample_distribution(int dist, double sigma, const uint64_t seed[4], siz
         }
     }
 }
+
+/* ---- G-lattice sampler: MatrixTrapdoor.cu:701-833 (sample) + 835-897 (scatter) ----------
+ * src: [rows*cols][L][n] coefficient domain; out: [(rows*dpt*L)*cols][L][n] coefficient domain,
+ * out row = row*dpt*L + tower*dpt + digit.  dpt = ceil(crt_bits / base_bits). */
+#define ORC_MAX_DIGITS 64
+static void gq_digits(Stream *rng, uint64_t value, uint64_t q, uint32_t bb, uint32_t k, double c, int64_t *out) {
+    uint64_t base = (uint64_t)1 << bb;
+    double base_f = (double)base, sigma = c / (base_f + 1.0), kf = (double)k;
+    int64_t m_digits[ORC_MAX_DIGITS], v_digits[ORC_MAX_DIGITS], z[ORC_MAX_DIGITS];
+    double l[ORC_MAX_DIGITS], h[ORC_MAX_DIGITS], c_vec[ORC_MAX_DIGITS], p[ORC_MAX_DIGITS], a[ORC_MAX_DIGITS],
+        zf[ORC_MAX_DIGITS];
+    uint64_t t = q, v = value % q;
+    for (uint32_t i = 0; i < k; i++) {
+        m_digits[i] = (int64_t)(t % base);
+        t /= base;
+        v_digits[i] = (int64_t)(v % base);
+        v /= base;
+    }
+    l[0] = sqrt(base_f * (1.0 + 1.0 / kf) + 1.0);
+    for (uint32_t i = 1; i < k; i++) l[i] = sqrt(base_f * (1.0 + 1.0 / (kf - (double)i)));
+    h[0] = 0.0;
+    for (uint32_t i = 1; i < k; i++) h[i] = sqrt(base_f * (1.0 - 1.0 / (kf - (double)(i - 1))));
+    c_vec[0] = (double)m_digits[0] / base_f;
+    for (uint32_t i = 1; i < k; i++) c_vec[i] = (c_vec[i - 1] + (double)m_digits[i]) / base_f;
+    for (uint32_t i = 0; i < k; i++) zf[i] = sigma * standard_normal(rng);
+    for (uint32_t i = 0; i + 1 < k; i++) p[i] = l[i] * zf[i] + h[i + 1] * zf[i + 1];
+    p[k - 1] = h[k - 1] * zf[k - 1];
+    a[0] = ((double)v_digits[0] - p[0]) / base_f;
+    for (uint32_t i = 1; i < k; i++) a[i] = (a[i - 1] + (double)v_digits[i] - p[i]) / base_f;
+    uint32_t last = k - 1;
+    z[last] = integer_karney(rng, -a[last] / c_vec[last], sigma / c_vec[last]);
+    for (uint32_t i = 0; i < k; i++) a[i] += (double)z[last] * c_vec[i];
+    for (uint32_t i = 0; i < last; i++) z[i] = integer_karney(rng, -a[i], sigma);
+    for (uint32_t i = 0; i < k; i++) {
+        int64_t b = (int64_t)base;
+        if (k == 1) out[i] = b * z[0] + m_digits[0] * z[0] + v_digits[0];
+        else if (i == 0) out[i] = b * z[0] + m_digits[0] * z[last] + v_digits[0];
+        else if (i < last) out[i] = b * z[i] - z[i - 1] + m_digits[i] * z[last] + v_digits[i];
+        else out[i] = m_digits[last] * z[last] - z[last - 1] + v_digits[last];
+    }
+}
+
+void orc_gauss_samp_gq(const uint64_t *src, size_t rows, size_t cols, size_t n, uint32_t L, const uint64_t *moduli,
+                       uint32_t crt_bits, uint32_t base_bits, double c, const uint64_t seed[4], uint64_t *out) {
+    const uint32_t k = (crt_bits + base_bits - 1) / base_bits;
+    const size_t ell = (size_t)k * L;
+#pragma omp parallel for schedule(static)
+    for (size_t poly = 0; poly < rows * cols; poly++) {
+        size_t row = poly / cols, col = poly % cols;
+        for (uint32_t tower = 0; tower < L; tower++)
+            for (size_t i = 0; i < n; i++) {
+                Stream rng;
+                int64_t digits[ORC_MAX_DIGITS];
+                stream_init(&rng, seed, (uint64_t)tower + 1, poly + 1, i + 1, 0x6761646765746731ULL);
+                gq_digits(&rng, src[(poly * L + tower) * n + i], moduli[tower], base_bits, k, c, digits);
+                for (uint32_t dg = 0; dg < k; dg++) {
+                    size_t out_poly = (row * ell + (size_t)tower * k + dg) * cols + col;
+                    for (uint32_t l = 0; l < L; l++) out[(out_poly * L + l) * n + i] = signed_mod(digits[dg], moduli[l]);
+                }
+            }
+    }
+}
+
+/* ---- perturbation p1 ------------------------------------------------------------------
+ * MatrixTrapdoor.cu:95-198 (factorisation, per coefficient, limb 0 of A, B, D centred) and
+ * :200-277 (conditional sampling), :674-699 (reduction into every limb).
+ * a, b, dm: [d*d][L][n] coefficient domain; tp2: [2d*cols][L][n]; out likewise.
+ * `sigma` here is the sampler's c (src/sampler/trapdoor/gpu.rs:145-169). */
+void orc_sample_p1(const uint64_t *a, const uint64_t *b, const uint64_t *dm, const uint64_t *tp2, size_t d, size_t cols,
+                   size_t n, uint32_t L, const uint64_t *moduli, double sigma, double s, double dgg_stddev,
+                   const uint64_t seed[4], uint64_t *out) {
+    const size_t m = 2 * d;
+    const uint64_t q0 = moduli[0];
+    const double sigma2 = sigma * sigma, s2 = s * s, fallback_var = dgg_stddev * dgg_stddev, eps = 1e-9;
+    const double c_scale = -(sigma * sigma) / (s * s - sigma * sigma);
+#pragma omp parallel
+    {
+        double *cov = malloc(m * m * sizeof(double)), *upd = calloc(m * m, sizeof(double)), *sd = malloc(m * sizeof(double)),
+               *mean = malloc(m * sizeof(double));
+        int64_t *zs = malloc(m * sizeof(int64_t));
+#pragma omp for schedule(static)
+        for (size_t ci = 0; ci < n; ci++) {
+#define AT(M, i, j) ((double)centered((M)[(((i) * d + (j)) * L) * n + ci], q0))
+            for (size_t i = 0; i < d; i++)
+                for (size_t j = 0; j < d; j++) {
+                    cov[i * m + j] = -sigma2 * AT(a, i, j) + (i == j ? s2 : 0.0);
+                    cov[(i + d) * m + (j + d)] = -sigma2 * AT(dm, i, j) + (i == j ? s2 : 0.0);
+                    cov[i * m + (j + d)] = -sigma2 * AT(b, i, j);
+                    cov[(i + d) * m + j] = -sigma2 * AT(b, j, i);
+                }
+#undef AT
+            for (long t = (long)m - 1; t >= 0; --t) {
+                double var = cov[t * m + t];
+                if (!(var > eps)) var = fallback_var;
+                sd[t] = sqrt(var);
+                for (long i = 0; i < t; i++) upd[t * m + i] = cov[i * m + t] / var;
+                for (long i = 0; i < t; i++)
+                    for (long j = 0; j <= i; j++) {
+                        double u = cov[i * m + j] - upd[t * m + i] * (upd[t * m + j] * var);
+                        cov[i * m + j] = u;
+                        cov[j * m + i] = u;
+                    }
+            }
+            for (size_t col = 0; col < cols; col++) {
+                Stream rng;
+                stream_init(&rng, seed, col + 1, ci + 1, 0, 0x7065727475726231ULL);
+                for (size_t r = 0; r < m; r++) mean[r] = c_scale * (double)centered(tp2[((r * cols + col) * L) * n + ci], q0);
+                for (long t = (long)m - 1; t >= 0; --t) {
+                    double mu = mean[t];
+                    zs[t] = integer_karney(&rng, mu, sd[t]);
+                    double delta = (double)zs[t] - mu;
+                    for (long i = 0; i < t; i++) mean[i] += upd[t * m + i] * delta;
+                }
+                for (size_t r = 0; r < m; r++)
+                    for (uint32_t l = 0; l < L; l++) out[((r * cols + col) * L + l) * n + ci] = signed_mod(zs[r], moduli[l]);
+            }
+        }
+        free(cov); free(upd); free(sd); free(mean); free(zs);
+    }
+}

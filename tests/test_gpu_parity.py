@@ -277,7 +277,7 @@ def test_error_paths(mx):
     assert L.gpu_matrix_mul(out.raw, A.raw, Bc.raw) != 0  # requires EVAL (MatrixArith.cu:2863-2866)
     assert L.gpu_matrix_copy_block(out.raw, A.raw, 0, 0, 0, 2, 2, 2) != 0  # out of range
     seed = ffi.GpuRngSeed()
-    assert L.gpu_matrix_sample_distribution(out.raw, 0, 0.0, seed) != 0  # outside the hot path: fails loudly
+    assert L.gpu_matrix_sample_distribution(out.raw, 9, 0.0, seed) != 0  # invalid dist_type (MatrixSampling.cu:424-427)
     empty = mx.GpuDCRTPolyMatrix(params, 0, 3)
     assert empty.to_rns().shape == (0, 3, 2, 128)
     assert (mx.GpuDCRTPolyMatrix(params, 2, 0) * mx.GpuDCRTPolyMatrix(params, 0, 3)).to_rns().any() == False  # noqa: E712
