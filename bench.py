@@ -352,6 +352,56 @@ def bench_bgg_chain(dist, device, depth_gates=8):
             "relation_holds": bool(ok), "timing": "host clock around the chain with a stream synchronize and barrier on both sides, max over ranks"}
 
 
+def bench_preimage(device, steps, warmup):
+    """configs[4] (C5): benches/bench_preimage_gpu.rs:34-55 — n=2^14, 10 x 24-bit limbs, base 2^12 (ell=20), d=1:
+    A 1x22, u 1x50, x 22x50.  One step = the whole Gaussian preimage (p2, T p2, p1, A p, G-lattice z, [R;E;I] z),
+    every integer drawn on the device; verified by A x == u.  The reference's CUDA library runs the same calls beside it."""
+    from mxx_b200 import GpuDCRTPolyMatrix as M, GpuDCRTPolyParams, ffi
+    from mxx_b200.trapdoor import GpuDCRTPolyTrapdoorSampler
+
+    cfg = {"n": 1 << 14, "depth": 10, "bits": 24, "bb": 12, "d": 1, "cols": 50}
+    sigma = 4.578
+
+    def run(lib, reps, warm):
+        params, _ = make_params(cfg, device) if lib is None else (None, None)
+        if lib is not None:
+            from mxx_b200 import standard_moduli
+
+            params = GpuDCRTPolyParams(cfg["n"], standard_moduli(cfg["n"], cfg["depth"], cfg["bits"]), cfg["bb"], gpu_ids=(device,), library=lib)
+        sampler = GpuDCRTPolyTrapdoorSampler(params, sigma)
+        td, a = sampler.trapdoor(params, cfg["d"], seed=[1, 2, 3, 4])
+        u = M.sample_distribution(params, cfg["d"], cfg["cols"], 0, 0.0, [5, 6, 7, 8])
+        L = lib or ffi.lib()
+        x = None
+        for i in range(warm):
+            x = sampler.preimage(params, td, a, u, seed=[9, i, 0, 0])
+        ffi.check_status(L.gpu_device_synchronize(), "gpu_device_synchronize", L)
+        t0 = time.perf_counter()
+        for i in range(reps):
+            x = sampler.preimage(params, td, a, u, seed=[10, i, 0, 0])
+        ffi.check_status(L.gpu_device_synchronize(), "gpu_device_synchronize", L)
+        dt = (time.perf_counter() - t0) / reps
+        x = sampler.preimage(params, td, a, u, seed=[11, 0, 0, 0])  # fixed seed: compared between the two libraries
+        ok = bool(a * x == u)
+        return dt, ok, x.to_rns()
+
+    dt, ok, mine = run(None, max(3, min(steps, 10)), max(1, min(warmup, 3)))
+    assert ok, "A * preimage != target"
+    res = {"workload": "C5 trapdoor preimage n=2^14 L=10x24-bit bb=12 d=1: A 1x22, u 1x50 -> x 22x50 (bench_preimage_gpu.rs:34-55)",
+           "ms_per_preimage": round(dt * 1e3, 3), "preimages_per_s": round(1.0 / dt, 2), "verified": "A*x == u (exact)",
+           "timing": "host wall clock around the whole call sequence + device synchronize (the sequence allocates and frees matrices)"}
+    path = os.path.join(ROOT, "oracle", "_ref", "libgpupoly_ref.so")
+    if os.path.exists(path):
+        try:
+            rdt, rok, theirs = run(ffi.bind(path, extensions=False), 3, 1)
+            res["reference_gpu"] = {"ms_per_preimage": round(rdt * 1e3, 3), "verified": rok, "kind": "reference",
+                                    "same_samples_as_ours": bool(np.array_equal(mine, theirs)),
+                                    "how": "the reference's cuda/ compiled for sm_100 (oracle/Makefile) driven by the same host sequence and seeds"}
+        except Exception as e:
+            res["reference_gpu"] = {"unavailable": repr(e)[:200]}
+    return res
+
+
 def int_peaks():
     """Register-resident microbenchmark of the butterfly / MAC primitives (tools/modmul_peak.cu): the measured
     INT-issue roofline denominators (butterflies/s, MACs/s) for the compute-bound kernels."""
@@ -526,6 +576,7 @@ def run_gpu(args):
             line["int_peaks"] = ip
             line["ntt"] = bench_ntt(device, max(3, min(args.steps, 20)), args.warmup, hbm_peak, ip)
             line["mul_decompose"] = bench_mul_decompose(device, max(3, min(args.steps, 20)), args.warmup, hbm_peak, ip)
+            line["preimage"] = bench_preimage(device, args.steps, args.warmup)
     if dist.rank == 0:
         emit(line)
     dist.close()

@@ -75,6 +75,9 @@ struct GpuContext {
     int ntt_block_override = 0;      // MXX_NTT_BLOCK_LOG
     bool smem_configured = false;  // >48 KB dynamic shared memory opted in for the NTT kernels
     uint32_t mac_fold = 1;   // products that fit one lazy accumulator between folds
+    // chunked host->device load pipeline (MatrixHostLoad.inl), built on first use
+    void *load_pipe = nullptr;
+    void (*load_pipe_free)(void *) = nullptr;
     size_t word_bytes() const { return wide ? 8 : 4; }
 };
 

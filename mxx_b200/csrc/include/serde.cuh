@@ -10,8 +10,9 @@
 
 namespace gp {
 
-template <typename T, bool BITREV>
-__global__ void pack_kernel(T *__restrict__ dst, const uint64_t *__restrict__ src, size_t total, uint32_t logn) {
+// S = source word type: u64 (the ABI's words) or u32 (words already narrowed on the host, MatrixHostLoad.inl)
+template <typename T, typename S, bool BITREV>
+__global__ void pack_kernel(T *__restrict__ dst, const S *__restrict__ src, size_t total, uint32_t logn) {
     const size_t step = (size_t)gridDim.x * GP_NT;
     const uint32_t mask = (1u << logn) - 1;
     for (size_t i = (size_t)blockIdx.x * GP_NT + GP_TID; i < total; i += step) {

@@ -58,6 +58,7 @@ void free_context(GpuContext *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->load_pipe && ctx->load_pipe_free) ctx->load_pipe_free(ctx->load_pipe);
     if (ctx->d_fwd) cudaFree(ctx->d_fwd);
     if (ctx->d_inv) cudaFree(ctx->d_inv);
     if (ctx->d_limb) cudaFree(ctx->d_limb);

@@ -20,6 +20,7 @@
 
 #include "MatrixCommon.inl"
 #include "MatrixData.inl"
+#include "MatrixHostLoad.inl"
 #include "MatrixSerde.inl"
 #include "MatrixNTT.inl"
 #include "MatrixArith.inl"

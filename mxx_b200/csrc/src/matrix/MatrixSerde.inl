@@ -27,9 +27,9 @@ template <typename T>
 int launch_pack(GpuContext *ctx, T *dst, const uint64_t *src, size_t words, bool bitrev) {
     const unsigned threads = 256, grid = stride_grid(ctx, words, threads);
     if (bitrev)
-        gp::pack_kernel<T, true><<<grid, threads, 0, gp::cur(ctx)>>>(dst, src, words, (uint32_t)ctx->logN);
+        gp::pack_kernel<T, uint64_t, true><<<grid, threads, 0, gp::cur(ctx)>>>(dst, src, words, (uint32_t)ctx->logN);
     else
-        gp::pack_kernel<T, false><<<grid, threads, 0, gp::cur(ctx)>>>(dst, src, words, (uint32_t)ctx->logN);
+        gp::pack_kernel<T, uint64_t, false><<<grid, threads, 0, gp::cur(ctx)>>>(dst, src, words, (uint32_t)ctx->logN);
     gp::count_launch();
     GP_CHECK_LAUNCH("pack_kernel");
     return 0;
@@ -66,6 +66,14 @@ extern "C" int gpu_matrix_load_rns_batch(GpuMatrix *mat, const uint8_t *bytes, s
     if (bytes_per_poly < tight)
         return gp::set_error("bytes_per_poly too small in gpu_matrix_load_rns_batch");  // MatrixSerde.cu:622
     if (bind_device(ctx)) return 1;
+    if (bytes_per_poly == tight) {  // large u32-context loads: chunked two-lane pipeline (MatrixHostLoad.inl)
+        const int hs = load_hybrid(ctx, mat, (const uint64_t *)bytes, polys * mat->poly_words(), format == GPU_POLY_FORMAT_EVAL);
+        if (hs > 0) return hs;
+        if (hs == 0) {
+            mat->format = format;
+            return make_event_set(ctx, out_events);
+        }
+    }
     Scratch stage;
     if (stage.alloc(polys * tight, ctx->stream)) return 1;
     if (bytes_per_poly == tight)

@@ -301,3 +301,35 @@ def test_full_size_properties(mx, n, depth, bits, bb, r, d, c):
     # spot check of one output polynomial against the oracle
     one = S1.mul_decompose(other.slice_columns(0, 1)).to_rns()
     assert np.array_equal(one, plan.mul_decompose(S1.to_rns(), other.slice_columns(0, 1).to_rns(), bb))
+
+
+@pytest.mark.parametrize("pinned", [False, True])
+def test_large_load_chunked_pipeline(mx, pinned):
+    """Loads above 128 MB on a u32 context go through the chunked two-lane pipeline (MatrixHostLoad.inl): host threads narrow
+    chunks from the back while raw chunks are DMA'd from the front.  Same device contents as the single-DMA path, for both
+    formats (EVAL applies the bit-reversal per chunk), with a ragged last chunk, from pageable and from pinned memory."""
+    n, depth = 4096, 3
+    params, plan = setup(mx, n, depth, 24, 12)
+    rows, cols = 3, 487  # 1461 polys * 3 * 4096 = 17.95 M words: 8 full chunks + a tail
+    host = plan.uniform(rows, cols, seed=4242)
+    buf = None
+    if pinned:
+        buf = mx.PinnedBuffer(host.shape)
+        buf.array[...] = host
+        src = buf.array
+    else:
+        src = host
+    for is_ntt in (False, True):
+        m = mx.GpuDCRTPolyMatrix(params, rows, cols, depth - 1, is_ntt)
+        m.load_rns(src, m._fmt())
+        assert np.array_equal(m.to_rns(), host)
+        # the chunks really are where the rest of the library expects them: transform + product on a slice
+        if is_ntt:
+            a = m.slice(0, 1, 0, 3)
+            b = m.slice(0, 3, 484, 487)
+            assert np.array_equal((a * b).to_rns(), plan.mul(host[0:1, 0:3], host[0:3, 484:487]))
+        else:
+            m.ntt_in_place()
+            assert np.array_equal(m.slice(2, 3, 480, 487).to_rns(), plan.ntt(host[2:3, 480:487]))
+    if buf is not None:
+        buf.free()
