@@ -83,6 +83,9 @@ struct GpuContext {
 
 namespace gp {
 inline cudaStream_t cur(const GpuContext *ctx) { return tl_stream ? tl_stream : ctx->stream; }
+// Contexts that are alive.  A handle that outlives its context (host-language finalisers running in arbitrary order at
+// process exit) must not touch the freed context or its stream: *_destroy consult this before any CUDA call.
+bool context_alive(const GpuContext *ctx);
 }  // namespace gp
 
 struct GpuMatrix {

@@ -58,14 +58,20 @@ struct ChaChaStream {
         return (v << n) | (v >> (32 - n));
 #endif
     }
-    // the 20-round ChaCha permutation (RFC 8439 §2.3, without the feed-forward)
-    // (kept out of line: it is reached from every draw site of the rejection samplers)
-    static __host__ __device__ __noinline__ void permute(uint32_t *x) {
+    // the 20-round ChaCha permutation (RFC 8439 §2.3, without the feed-forward).  Kept out of line (it is reached
+    // from several draw sites) and run on a register copy: through the pointer every quarter-round step would be
+    // a local-memory round trip (62 % of the instructions of the first version, profiles/r01_ncu_sampler.txt).
+    static __host__ __device__ __noinline__ void permute(uint32_t *state) {
+        uint32_t x[16];
+#pragma unroll
+        for (int i = 0; i < 16; i++) x[i] = state[i];
 #pragma unroll
         for (int dr = 0; dr < 10; dr++) {
             GP_CC_QR(0, 4, 8, 12); GP_CC_QR(1, 5, 9, 13); GP_CC_QR(2, 6, 10, 14); GP_CC_QR(3, 7, 11, 15);
             GP_CC_QR(0, 5, 10, 15); GP_CC_QR(1, 6, 11, 12); GP_CC_QR(2, 7, 8, 13); GP_CC_QR(3, 4, 9, 14);
         }
+#pragma unroll
+        for (int i = 0; i < 16; i++) state[i] = x[i];
     }
     static GP_HD void sigma(uint32_t *x) {
         x[0] = 0x61707865u; x[1] = 0x3320646eu; x[2] = 0x79622d32u; x[3] = 0x6b206574u;
@@ -113,13 +119,14 @@ struct ChaChaStream {
         return v;
     }
     // uniform deviate in the open interval (0,1), 53 bits
-    GP_HD double unit() {
+    static GP_HD double to_unit(uint64_t w) {
         const double scale = 1.0 / 9007199254740992.0;
-        double u = (double)(next() >> 11) * scale;
+        double u = (double)(w >> 11) * scale;
         if (u <= 0.0) u = scale;
         else if (u >= 1.0) u = 1.0 - scale;
         return u;
     }
+    GP_HD double unit() { return to_unit(next()); }
     // uniform residue in [0, q): rejection below the largest multiple of q
     GP_HD uint64_t below(uint64_t q) {
         if (q == 0) return 0;
@@ -154,69 +161,126 @@ GP_HD int64_t centred(uint64_t x, uint64_t q) {
 }
 
 // ---- Karney's exact discrete Gaussian --------------------------------------------------
-// H: true with probability exp(-1/2)
-GP_HD bool karney_h(ChaChaStream &g) {
-    double a = g.unit();
-    if (!(a < 0.5)) return true;
-    for (;;) {
-        const double b = g.unit();
-        if (!(b < a)) return false;
-        a = g.unit();
-        if (!(a < b)) return true;
-    }
-}
-// G: k >= 0 with probability exp(-k/2)(1 - exp(-1/2)); capped like the reference
-GP_HD int32_t karney_g(ChaChaStream &g) {
-    int32_t k = 0;
-    while (karney_h(g)) {
-        if (++k > 1024) break;
-    }
-    return k;
-}
-// P: true with probability exp(-n/2)
-GP_HD bool karney_p(ChaChaStream &g, int32_t n) {
-    while (n-- && karney_h(g)) {
-    }
-    return n < 0;
-}
-// B: true with probability exp(-x(2k+x)/(2k+2))
-GP_HD bool karney_b(ChaChaStream &g, int32_t k, double x) {
-    const double m = (double)(2 * k + 2);
-    double y = x;
-    int32_t n = 0;
-    for (;; ++n) {
-        const double z = g.unit();
-        if (!(z < y)) break;
-        const double r = g.unit();
-        if (!(r < (2.0 * (double)k + x) / m)) break;
-        y = z;
-        if (n > 4096) break;
-    }
-    return (n & 1) == 0;
-}
+// Algorithms H (true w.p. e^{-1/2}), G (k >= 0 w.p. e^{-k/2}(1 - e^{-1/2})), P (true w.p. e^{-n/2}),
+// B (true w.p. e^{-x(2k+x)/(2k+2)}) and the integer sampler built on them, with the reference's iteration caps and
+// Box-Muller fall-back (MatrixSampling.cu:31-160) — written as a state machine that consumes exactly ONE stream
+// word per step().  Why: as nested rejection loops the lanes of a warp sit at different program points almost all
+// the time (3.6 of 32 lanes active per instruction and a ChaCha permutation per lane per block, ncu
+// profiles/r01_ncu_sampler.txt).  With one word per step every lane of a warp draws at the same instruction,
+// key-stream blocks are refilled by all lanes together, and only the few-instruction case bodies diverge.
+// The sequence of words each decision consumes is unchanged, so samples are identical to the nested-loop form.
+struct KarneyMachine {
+    enum : uint32_t { kGH0, kGH1, kGH2, kPH0, kPH1, kPH2, kSign, kJ, kB0, kB1, kFb1, kFb2, kDone };
+    uint32_t st;
+    int32_t k, n, h, bn, tries;
+    double mean, sd, hv, x, x0, y, z;
+    int64_t i0, j, sgn, span, result;
 
-// integer z ~ D_{Z, stddev, mean}
-GP_HD int64_t karney_integer(ChaChaStream &g, double mean, double stddev) {
-    if (!(stddev > 0.0) || !isfinite(mean) || !isfinite(stddev)) return (int64_t)llround(mean);
-    const int64_t span = (int64_t)ceil(stddev);
-    if (span <= 0) return (int64_t)llround(mean);
-    for (int tries = 0; tries < (1 << 16); ++tries) {
-        const int32_t k = karney_g(g);
-        if (!karney_p(g, k * (k - 1))) continue;
-        const int64_t s = (g.next() & 1ULL) ? 1 : -1;
-        const double di0 = stddev * (double)k + (double)s * mean;
-        const int64_t i0 = (int64_t)ceil(di0);
-        const double x0 = ((double)i0 - di0) / stddev;
-        const int64_t j = (int64_t)(g.next() % (uint64_t)span);
-        const double x = x0 + (double)j / stddev;
-        if (!(x < 1.0) || (x == 0.0 && s < 0 && k == 0)) continue;
-        int32_t h = k + 1;
-        while (h-- > 0 && karney_b(g, k, x)) {
-        }
-        if (h >= 0) continue;
-        return s * (i0 + j);
+    GP_HD bool done() const { return st == kDone; }
+    GP_HD void finish(int64_t r) { result = r, st = kDone; }
+    GP_HD void begin(double mean_, double sd_) {
+        mean = mean_, sd = sd_, tries = 0;
+        if (!(sd > 0.0) || !isfinite(mean) || !isfinite(sd)) return finish((int64_t)llround(mean));
+        span = (int64_t)ceil(sd);
+        if (span <= 0) return finish((int64_t)llround(mean));
+        restart();
     }
-    return (int64_t)llround(mean + stddev * g.normal());
+    // top of the rejection loop (65536 attempts, then the continuous fall-back)
+    GP_HD void restart() {
+        if (tries >= (1 << 16)) { st = kFb1; return; }
+        ++tries, k = 0, st = kGH0;
+    }
+    // P: `while (n-- && H()) {}` accepted when n ran out
+    GP_HD void p_check() {
+        if (n == 0) st = kSign;
+        else --n, st = kPH0;
+    }
+    // `h = k + 1; while (h-- > 0 && B()) {}` accepted when h ran out
+    GP_HD void b_check() {
+        if (h > 0) --h, y = x, bn = 0, st = kB0;
+        else finish(sgn * (i0 + j));
+    }
+    GP_HD void h_result(bool r, bool in_g) {
+        if (in_g) {
+            if (r && ++k <= 1024) { st = kGH0; return; }
+            n = k * (k - 1);
+            p_check();
+        } else if (r) p_check();
+        else restart();
+    }
+    GP_HD void b_result() {
+        if ((bn & 1) == 0) b_check();
+        else restart();
+    }
+    GP_HD void step(uint64_t w) {
+        const double u = ChaChaStream::to_unit(w);
+        switch (st) {
+            case kGH0:
+            case kPH0:  // H: a = U; !(a < 1/2) -> true
+                hv = u;
+                if (!(u < 0.5)) h_result(true, st == kGH0);
+                else st += 1;
+                break;
+            case kGH1:
+            case kPH1:  // b = U; !(b < a) -> false
+                if (!(u < hv)) h_result(false, st == kGH1);
+                else hv = u, st += 1;
+                break;
+            case kGH2:
+            case kPH2:  // a = U; !(a < b) -> true
+                if (!(u < hv)) h_result(true, st == kGH2);
+                else hv = u, st -= 1;
+                break;
+            case kSign: {
+                sgn = (w & 1ULL) ? 1 : -1;
+                const double di0 = sd * (double)k + (double)sgn * mean;
+                i0 = (int64_t)ceil(di0);
+                x0 = ((double)i0 - di0) / sd;
+                st = kJ;
+                break;
+            }
+            case kJ:
+                j = (int64_t)(w % (uint64_t)span);
+                x = x0 + (double)j / sd;
+                if (!(x < 1.0) || (x == 0.0 && sgn < 0 && k == 0)) restart();
+                else h = k + 1, b_check();
+                break;
+            case kB0:  // z = U; !(z < y) ends B
+                z = u;
+                if (!(u < y)) b_result();
+                else st = kB1;
+                break;
+            case kB1:  // r = U; !(r < (2k + x) / (2k + 2)) ends B
+                if (!(u < (2.0 * (double)k + x) / (double)(2 * k + 2))) b_result();
+                else {
+                    y = z;
+                    if (bn > 4096) b_result();
+                    else ++bn, st = kB0;
+                }
+                break;
+            case kFb1:
+                hv = u, st = kFb2;
+                break;
+            case kFb2: {
+                const double r = sqrt(-2.0 * log(hv));
+                const double theta = 6.283185307179586476925286766559 * u;
+                finish((int64_t)llround(mean + sd * (r * cos(theta))));
+                break;
+            }
+            default:
+                break;
+        }
+    }
+};
+
+// integer z ~ D_{Z, stddev, mean}.  (Consecutive draws of one stream are separate calls: the lanes of a warp meet again
+// between them.  A variant that chained the draws through a task object holding pointers to the caller's local arrays
+// faulted on the device with nvcc 12.9 although the same code is correct on the host — tools/sampler_lab.cu.)
+GP_HD int64_t karney_integer(ChaChaStream &g, double mean, double stddev) {
+    KarneyMachine km;
+    km.begin(mean, stddev);
+    while (!km.done()) km.step(g.next());
+    return km.result;
 }
 
 // ---- one coefficient of gpu_matrix_sample_distribution ----------------------------------
@@ -364,7 +428,6 @@ GP_HD void p1_sample_column(LoadTp2 centred_tp2, const Seed256 &seed, uint32_t m
         const double mu = mean[(size_t)t * st];
         const int64_t zt = karney_integer(g, mu, sd[(size_t)t * n + coeff]);
         zs[(size_t)t * st] = zt;
-        if (t == 0) break;
         const double delta = (double)zt - mu;
         for (int i = 0; i < t; i++) mean[(size_t)i * st] += GP_UPD(t, i) * delta;
     }

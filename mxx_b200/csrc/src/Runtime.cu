@@ -54,8 +54,15 @@ void upload_tables(GpuContext *ctx) {
     chk(cudaMemcpy(d_lc, t.limb.data(), t.limb.size() * sizeof(t.limb[0]), cudaMemcpyHostToDevice));
 }
 
+std::mutex g_live_mutex;
+std::unordered_set<const GpuContext *> g_live;
+
 void free_context(GpuContext *ctx) {
     if (!ctx) return;
+    {
+        std::lock_guard<std::mutex> g(g_live_mutex);
+        g_live.erase(ctx);
+    }
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     if (ctx->load_pipe && ctx->load_pipe_free) ctx->load_pipe_free(ctx->load_pipe);
@@ -76,6 +83,13 @@ void free_context(GpuContext *ctx) {
 constexpr size_t kMaxLimbs = 64;  // Runtime.cuh:51
 constexpr size_t kMaxGpus = 8;    // Runtime.cuh:52
 }  // namespace
+
+namespace gp {
+bool context_alive(const GpuContext *ctx) {
+    std::lock_guard<std::mutex> g(g_live_mutex);
+    return g_live.count(ctx) != 0;
+}
+}  // namespace gp
 
 extern "C" {
 
@@ -144,6 +158,10 @@ int gpu_context_create(uint32_t logN, uint32_t L, uint32_t dnum, const uint64_t 
         GP_CUDA(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming), "cudaEventCreate(fork)");
         if (ctx->wide) upload_tables<uint64_t>(ctx);
         else upload_tables<uint32_t>(ctx);
+        {
+            std::lock_guard<std::mutex> g(g_live_mutex);
+            g_live.insert(ctx);
+        }
         *out_ctx = ctx;
         return 0;
     } catch (const std::exception &e) {

@@ -73,7 +73,7 @@ extern "C" int gpu_matrix_create(GpuContext *ctx, int level, size_t rows, size_t
 
 extern "C" void gpu_matrix_destroy(GpuMatrix *mat) {
     if (!mat) return;
-    if (mat->data && mat->ctx) {
+    if (mat->data && mat->ctx && gp::context_alive(mat->ctx)) {
         cudaSetDevice(mat->ctx->device);
         cudaFreeAsync(mat->data, mat->ctx->stream);  // ordered after every use: all work is on this stream
     }

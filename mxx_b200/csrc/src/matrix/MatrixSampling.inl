@@ -200,7 +200,7 @@ extern "C" int gpu_matrix_create_p1_covariance_cache(const GpuMatrix *a_mat, con
 
 extern "C" void gpu_matrix_destroy_p1_covariance_cache(GpuP1CovarianceCache *cache) {
     if (!cache) return;
-    if (cache->ctx && (cache->sd || cache->upd)) {
+    if (cache->ctx && (cache->sd || cache->upd) && gp::context_alive(cache->ctx)) {
         cudaSetDevice(cache->ctx->device);
         if (cache->sd) cudaFreeAsync(cache->sd, cache->ctx->stream);
         if (cache->upd) cudaFreeAsync(cache->upd, cache->ctx->stream);

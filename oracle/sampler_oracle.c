@@ -389,3 +389,14 @@ void orc_sample_p1(const uint64_t *a, const uint64_t *b, const uint64_t *dm, con
         free(cov); free(upd); free(sd); free(mean); free(zs);
     }
 }
+
+/* how many u64 words of its stream each Karney sample consumed (sizing of the device-side key-stream prefetch) */
+void orc_karney_draw_counts(const uint64_t seed[4], double mean, double stddev, size_t count, uint32_t *out) {
+    for (size_t i = 0; i < count; i++) {
+        Stream s;
+        stream_init(&s, seed, i + 1, 1, 0, 0x6f70656e66686532ULL);
+        (void)integer_karney(&s, mean, stddev);
+        uint64_t blocks = ((uint64_t)s.w[0] | ((uint64_t)s.w[1] << 32)) - (i + 1);
+        out[i] = (uint32_t)((blocks - 1) * 8 + s.idx);
+    }
+}
