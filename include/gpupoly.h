@@ -102,8 +102,14 @@ int gpu_matrix_fill_small_decomposed_identity_chunk(GpuMatrix *out, const GpuMat
 int gpu_matrix_decompose_base(const GpuMatrix *src, uint32_t base_bits, GpuMatrix *out);       /* gpu.rs:176-180; MatrixDecompose.cu:892-1342 */
 int gpu_matrix_decompose_base_small(const GpuMatrix *src, uint32_t base_bits, GpuMatrix *out); /* gpu.rs:181-185 */
 
-/* ---- samplers / trapdoor (SURVEY §8f "next" rows; exported so the Rust crate links;
- *      return non-zero with a message until built) ---- */
+/* ---- samplers / trapdoor: replace cuda/src/matrix/MatrixSampling.cu, MatrixTrapdoor.cu, ChaCha.cu ----
+ * Every integer is drawn on the device from ChaCha20 streams keyed by the GpuRngSeed (ChaCha.cu:109-166); for a given
+ * seed the result is, residue for residue, the matrix the reference library returns (tests/test_samplers.py).
+ * gauss_samp: out is (rows*ell) x cols created in the format wanted back; an EVAL src is INTT'd in place
+ *   (MatrixTrapdoor.cu:1739-1746).  sample_distribution(_columns): dist_type = GPU_MATRIX_DIST_*, result EVAL;
+ *   the _columns form fills columns [col_offset, col_offset + out->cols) of the full_ncol-wide matrix the seed defines.
+ * p1 cache: A, B, D are d x d coefficient-form matrices (limb 0 is read, centred); sample_p1_full_cached: tp2 is
+ *   2d x cols in coefficient form, result EVAL (MatrixTrapdoor.cu:2159-2474, 2476-2918). */
 int gpu_matrix_gauss_samp_gq_arb_base(GpuMatrix *src, uint32_t base_bits, double c, double dgg_stddev,
                                       GpuRngSeed seed, GpuMatrix *out); /* gpu.rs:186-193 */
 int gpu_matrix_create_p1_covariance_cache(const GpuMatrix *a_mat, const GpuMatrix *b_mat, const GpuMatrix *d_mat,
