@@ -68,6 +68,9 @@ struct GpuContext {
     void *d_fwd = nullptr;   // [L][N] TwPair: psi^bitrev(i)
     void *d_inv = nullptr;   // [L][N] TwPair: psi^-bitrev(i)
     void *d_limb = nullptr;  // [L] LimbConst
+    // FP64-pipe NTT tables (TwPair<F64>, LimbConst<F64>), only for u64-word contexts with every modulus < 2^51
+    void *d_fwd_f64 = nullptr, *d_inv_f64 = nullptr, *d_limb_f64 = nullptr;
+    bool f64_ntt = false;  // MXX_NTT_F64=0 keeps the integer butterflies
     void *d_garner = nullptr;  // [L][L] u64: q_j^-1 mod q_i (compact wire format), built on first use
     std::mutex lazy_mutex;
     bool nocsub = false;             // forward NTT without conditional subtractions (36*qmax fits the word)

@@ -4,6 +4,7 @@
 // least primitive root g (cuda/src/Runtime.cu:121-165), psi = g^((p-1)/2n) (:167-190),
 // n^-1 (:282-319).
 #pragma once
+#include <string.h>
 #include <stdint.h>
 
 #include <stdexcept>
@@ -117,6 +118,37 @@ Tables<T> build_tables(int logN, const std::vector<uint64_t> &moduli, const std:
     }
     return t;
 }
+
+// The same tables for the FP64-pipe kernels (modarith.cuh F64): twiddles as doubles with their quotients w/q;
+// LimbConst<F64> reuses the generic field names — q2 carries 1/q (the F64 butterflies need no 2q), one_s too.
+inline Tables<F64> f64_tables(const Tables<uint64_t> &t) {
+    Tables<F64> r;
+    const size_t L = t.limb.size(), per = L ? t.fwd.size() / L : 0;
+    r.fwd.resize(t.fwd.size());
+    r.inv.resize(t.inv.size());
+    r.limb.resize(L);
+    for (size_t l = 0; l < L; ++l) {
+        const double q = (double)t.limb[l].q;
+        for (size_t i = 0; i < per; ++i) {
+            r.fwd[l * per + i] = {(double)t.fwd[l * per + i].w, (double)t.fwd[l * per + i].w / q};
+            r.inv[l * per + i] = {(double)t.inv[l * per + i].w, (double)t.inv[l * per + i].w / q};
+        }
+        LimbConst<F64> &c = r.limb[l];
+        memset(&c, 0, sizeof(c));
+        c.q.v = q;
+        c.q2.v = 1.0 / q;
+        c.one_s.v = 1.0 / q;
+        c.ninv.v = (double)t.limb[l].ninv;
+        c.ninv_s.v = (double)t.limb[l].ninv / q;
+        c.nw.v = (double)t.limb[l].nw;
+        c.nw_s.v = (double)t.limb[l].nw / q;
+        c.mu64 = t.limb[l].mu64;
+        c.bits = t.limb[l].bits;
+    }
+    return r;
+}
+// FP64-pipe NTT: u64-word contexts whose moduli all stay below 2^51 (4q < 2^53 keeps every intermediate exact)
+inline bool f64_ok(uint64_t qmax, bool wide) { return wide && qmax < ((uint64_t)1 << 51); }
 
 // products that fit one lazy accumulator (2^64 for u32 words, 2^128 for u64) on top of a folded residue
 inline uint32_t mac_fold_terms(uint64_t qmax, bool wide) {

@@ -34,6 +34,20 @@ template <typename T> struct TwPair;
 template <> struct __align__(8) TwPair<uint32_t> { uint32_t w, ws; };
 template <> struct __align__(16) TwPair<uint64_t> { uint64_t w, ws; };
 
+// ---- residues as doubles ---------------------------------------------------------------------------------
+// F64 is the working type of the FP64-pipe NTT for moduli below 2^51 that are stored as u64 words: the value is
+// an exact integer held in a double (|v| < 2^53), signed and lazily reduced.  In GLOBAL memory an F64 pointer still
+// addresses the u64 residue words (the kernels convert on load / store); in registers and shared memory it is the
+// double.  Why: the 64-bit Shoup butterfly costs ~22 passes of the integer multiply pipe, the same butterfly in
+// doubles is 11-13 FP64 operations on a pipe that issues 64 per clock per SM on B200 (tools/fp64_bfly_lab.cu:
+// 1.6e12 butterflies/s against 0.82e12).
+struct F64 {
+    double v;
+};
+template <> struct __align__(16) TwPair<F64> { double w, ws; };  // w in [0, q) and ws = w / q
+template <typename T> struct is_f64 { static constexpr bool value = false; };
+template <> struct is_f64<F64> { static constexpr bool value = true; };
+
 // Per-limb constants, one entry per CRT limb, resident in global memory.
 template <typename T> struct LimbConst {
     T q;             // modulus
@@ -94,6 +108,45 @@ GP_HD uint64_t red128(uint64_t hi, uint64_t lo, const LimbConst<uint64_t> &c) {
     uint64_t s = a + b;                                              // < 3q < 2^64
     s = csub(s, c.q2);
     return csub(s, c.q);
+}
+
+// 1.5 * 2^52: adding and subtracting it rounds |x| < 2^51 to the nearest integer
+#define GP_F64_MAGIC 6755399441055744.0
+GP_HD double f64_mul(double a, double b) {
+#ifdef __CUDA_ARCH__
+    return __dmul_rn(a, b);  // never contracted into a neighbouring add
+#else
+    return a * b;
+#endif
+}
+GP_HD double f64_add(double a, double b) {
+#ifdef __CUDA_ARCH__
+    return __dadd_rn(a, b);
+#else
+    return a + b;
+#endif
+}
+// x - q * rint(x / q): any |x| < 2^53 -> |result| <= q/2 (+1 ulp of the quotient estimate); exact
+GP_HD double f64_renorm(double x, double q, double qinv) {
+    const double k = f64_add(fma(x, qinv, GP_F64_MAGIC), -GP_F64_MAGIC);
+    return fma(-k, q, x);
+}
+// y * w mod q for |y| <= 2^51 / 1 (so that |y * w / q| < 2^51), w in [0, q), wq = w / q rounded:
+// h + l = y * w exactly (l is the rounding error of the product); b = rint(y * wq) is within 1 of the true quotient;
+// c = h - b q is exact (|c| < 2^53 and an integer multiple of ulp(h)); result = c + l, |result| <= (1/2 + |y| 2^-53) q.
+GP_HD double f64_mulmod(double y, double w, double wq, double q) {
+    const double h = f64_mul(y, w);
+    const double l = fma(y, w, -h);
+    const double b = f64_add(fma(y, wq, GP_F64_MAGIC), -GP_F64_MAGIC);
+    const double c = fma(-b, q, h);
+    return f64_add(c, l);
+}
+// signed lazy value -> canonical residue in [0, q) as an integer word
+GP_HD uint64_t f64_canonical(double x, double q, double qinv) {
+    double r = f64_renorm(x, q, qinv);
+    if (r < 0.0) r += q;
+    if (r >= q) r -= q;
+    return (uint64_t)r;
 }
 
 // Lazy accumulator for sum_k a_k*b_k mod q.

@@ -42,6 +42,18 @@ template <typename T> struct PlainSrc {
     GP_HD T xform(T raw) const { return raw; }
     GP_HD T operator()(uint32_t i) const { return p[i]; }
 };
+// F64 working type (modarith.cuh): the words in memory are u64 integers below 8q (canonical, or lazily reduced by
+// the integer global passes that precede the block kernel for rings above one CTA); one conditional subtraction
+// keeps the converted value below 2^53
+template <> struct PlainSrc<F64> {
+    const F64 *p;
+    uint64_t q4;  // 4q
+    GP_HD F64 operator()(uint32_t i) const {
+        uint64_t r = reinterpret_cast<const uint64_t *>(p)[i];
+        if (r >= q4) r -= q4;
+        return F64{(double)r};
+    }
+};
 // Gadget digit of a coefficient-form residue, the fused load of decompose + NTT:
 // (x_t >> dg*bb) & mask, reduced into the target limb if needed
 // (semantics of cuda/src/matrix/MatrixDecompose.cu:93-113).

@@ -21,6 +21,8 @@
 //     no conditional subtraction at all (values grow by 2q per stage and the Shoup multiply
 //     accepts any word); one Shoup-by-one reduction at the final store brings them to [0, q).
 #pragma once
+#include <string.h>
+
 #include "modarith.cuh"
 #include "ntt.cuh"
 
@@ -69,7 +71,43 @@ template <int LOGB> struct SmemView<uint64_t, LOGB> {
         *reinterpret_cast<uint4 *>(hi + i) = make_uint4((uint32_t)(x[0] >> 32), (uint32_t)(x[1] >> 32), (uint32_t)(x[2] >> 32), (uint32_t)(x[3] >> 32));
     }
 };
-
+// doubles travel through shared memory as their bit patterns in the u64 two-plane layout
+GP_HD uint64_t f64_bits(double d) {
+#ifdef __CUDA_ARCH__
+    return (uint64_t)__double_as_longlong(d);
+#else
+    uint64_t u;
+    memcpy(&u, &d, 8);
+    return u;
+#endif
+}
+GP_HD double f64_from_bits(uint64_t u) {
+#ifdef __CUDA_ARCH__
+    return __longlong_as_double((long long)u);
+#else
+    double d;
+    memcpy(&d, &u, 8);
+    return d;
+#endif
+}
+template <int LOGB> struct SmemView<F64, LOGB> {
+    SmemView<uint64_t, LOGB> raw;
+    GP_HD explicit SmemView(void *base) : raw(base) {}
+    GP_HD F64 ld(uint32_t i) const { return F64{f64_from_bits(raw.ld(i))}; }
+    GP_HD void st(uint32_t i, F64 v) const { raw.st(i, f64_bits(v.v)); }
+    GP_HD void ld4(uint32_t i, F64 (&x)[4]) const {
+        uint64_t u[4];
+        raw.ld4(i, u);
+#pragma unroll
+        for (int j = 0; j < 4; j++) x[j].v = f64_from_bits(u[j]);
+    }
+    GP_HD void st4(uint32_t i, const F64 (&x)[4]) const {
+        uint64_t u[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) u[j] = f64_bits(x[j].v);
+        raw.st4(i, u);
+    }
+};
 
 // launch shape per block size (needed by the passes: loop trip counts are compile-time constants)
 template <typename T, int LOGB> struct FastCfg {
@@ -146,6 +184,20 @@ GP_HD void gst4(uint64_t *p, const uint64_t (&x)[4]) {
     *reinterpret_cast<ulonglong2 *>(p + 2) = make_ulonglong2(x[2], x[3]);
 }
 
+// F64: the words in global memory are integers (canonical residues on the way in)
+GP_HD void gld4(const F64 *p, F64 (&x)[4]) {
+    uint64_t u[4];
+    gld4(reinterpret_cast<const uint64_t *>(p), u);
+#pragma unroll
+    for (int j = 0; j < 4; j++) x[j].v = (double)u[j];
+}
+GP_HD void gst4(F64 *p, const F64 (&x)[4]) {  // x already canonical, see f_last
+    uint64_t u[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) u[j] = (uint64_t)x[j].v;
+    gst4(reinterpret_cast<uint64_t *>(p), u);
+}
+
 // unsigned min trick: x - m wraps to a huge value when x < m
 template <typename T> GP_HD T csub_min(T x, T m) {
     const T y = x - m;
@@ -175,6 +227,10 @@ template <int COUNT> GP_HD void load_tw(const TwPair<uint64_t> *__restrict__ p, 
 #pragma unroll
     for (int i = 0; i < COUNT; i++) w[i] = p[i];
 }
+template <int COUNT> GP_HD void load_tw(const TwPair<F64> *__restrict__ p, TwPair<F64> (&w)[COUNT]) {
+#pragma unroll
+    for (int i = 0; i < COUNT; i++) w[i] = p[i];
+}
 
 // ---- butterfly networks ---------------------------------------------------------------------
 // Forward (Cooley-Tukey): stage s pairs j and j + (R >> (s+1)); twiddle index (twbase << s) + u.
@@ -189,16 +245,30 @@ GP_HD void fwd_stage(T (&x)[1 << LOGR], const TwPair<T> *__restrict__ tw, uint32
 #pragma unroll
         for (int v = 0; v < half; v++) {
             const int j0 = u * 2 * half + v, j1 = j0 + half;
-            const T X = NOCSUB ? x[j0] : csub_min<T>(x[j0], q2);
-            const T t = mul_shoup_lazy<T>(x[j1], w[u].w, w[u].ws, q);
-            x[j0] = X + t;
-            x[j1] = X - t + q2;
+            if constexpr (is_f64<T>::value) {
+                // F64 (q2 carries 1/q): the multiplied leg is renormalised to |y| <= q/2, the other leg grows by
+                // < 0.63 q per stage and is renormalised at the entry of every net (fwd_net): < 4q < 2^53 throughout
+                const double t = f64_mulmod(f64_renorm(x[j1].v, q.v, q2.v), w[u].w, w[u].ws, q.v);
+                const double X = x[j0].v;
+                x[j0].v = f64_add(X, t);
+                x[j1].v = f64_add(X, -t);
+            } else {
+                const T X = NOCSUB ? x[j0] : csub_min<T>(x[j0], q2);
+                const T t = mul_shoup_lazy<T>(x[j1], w[u].w, w[u].ws, q);
+                x[j0] = X + t;
+                x[j1] = X - t + q2;
+            }
         }
     }
     if constexpr (S + 1 < LOGR) fwd_stage<T, LOGR, S + 1, NOCSUB>(x, tw, twbase, q, q2);
 }
 template <typename T, int LOGR, bool NOCSUB>
 GP_HD void fwd_net(T (&x)[1 << LOGR], const TwPair<T> *__restrict__ tw, uint32_t twbase, T q, T q2) {
+    if constexpr (is_f64<T>::value) {
+        static_assert(LOGR <= 5, "an F64 net may grow the unmultiplied leg for at most 5 stages");
+#pragma unroll
+        for (int j = 0; j < (1 << LOGR); j++) x[j].v = f64_renorm(x[j].v, q.v, q2.v);
+    }
     fwd_stage<T, LOGR, 0, NOCSUB>(x, tw, twbase, q, q2);
 }
 // Inverse (Gentleman-Sande): stage s pairs j and j + (1 << s); inputs and outputs in [0, 2q).
@@ -212,8 +282,13 @@ GP_HD void inv_stage(T (&x)[1 << LOGR], const TwPair<T> *__restrict__ tw, uint32
         for (int v = 0; v < (1 << S); v++) {
             const int j0 = v, j1 = j0 + (1 << S);
             const T X = x[j0], Y = x[j1];
-            x[j0] = mul_shoup_lazy<T>(X + Y, c.ninv, c.ninv_s, q);
-            x[j1] = mul_shoup_lazy<T>(X - Y + q2, c.nw, c.nw_s, q);
+            if constexpr (is_f64<T>::value) {
+                x[j0].v = f64_mulmod(f64_renorm(f64_add(X.v, Y.v), q.v, q2.v), c.ninv.v, c.ninv_s.v, q.v);
+                x[j1].v = f64_mulmod(f64_renorm(f64_add(X.v, -Y.v), q.v, q2.v), c.nw.v, c.nw_s.v, q.v);
+            } else {
+                x[j0] = mul_shoup_lazy<T>(X + Y, c.ninv, c.ninv_s, q);
+                x[j1] = mul_shoup_lazy<T>(X - Y + q2, c.nw, c.nw_s, q);
+            }
         }
     } else {
         TwPair<T> w[groups];
@@ -224,8 +299,16 @@ GP_HD void inv_stage(T (&x)[1 << LOGR], const TwPair<T> *__restrict__ tw, uint32
             for (int v = 0; v < (1 << S); v++) {
                 const int j0 = u * (2 << S) + v, j1 = j0 + (1 << S);
                 const T X = x[j0], Y = x[j1];
-                x[j0] = csub_min<T>(X + Y, q2);
-                x[j1] = mul_shoup_lazy<T>(X - Y + q2, w[u].w, w[u].ws, q);
+                if constexpr (is_f64<T>::value) {
+                    // the sum leg doubles per stage: renormalised on odd stages and at the end of the net, so that
+                    // nets hand over |x| <= 0.63 q and nothing exceeds 4q < 2^53 in between
+                    const double sum = f64_add(X.v, Y.v);
+                    x[j0].v = ((S & 1) || S == LOGR - 1) ? f64_renorm(sum, q.v, q2.v) : sum;
+                    x[j1].v = f64_mulmod(f64_renorm(f64_add(X.v, -Y.v), q.v, q2.v), w[u].w, w[u].ws, q.v);
+                } else {
+                    x[j0] = csub_min<T>(X + Y, q2);
+                    x[j1] = mul_shoup_lazy<T>(X - Y + q2, w[u].w, w[u].ws, q);
+                }
             }
         }
     }
@@ -254,28 +337,52 @@ GP_HD Tw3<uint64_t> load_tw3(const TwPair<uint64_t> *__restrict__ tw, uint32_t t
     r.b1 = tw[2 * (size_t)tb + 1];
     return r;
 }
+GP_HD Tw3<F64> load_tw3(const TwPair<F64> *__restrict__ tw, uint32_t tb) {
+    Tw3<F64> r;
+    r.a = tw[tb];
+    r.b0 = tw[2 * (size_t)tb];
+    r.b1 = tw[2 * (size_t)tb + 1];
+    return r;
+}
 template <typename T, bool NOCSUB> GP_HD void fwd_bfly(T &x0, T &x1, const TwPair<T> &w, T q, T q2) {
-    const T X = NOCSUB ? x0 : csub_min<T>(x0, q2);
-    const T t = mul_shoup_lazy<T>(x1, w.w, w.ws, q);
-    x0 = X + t;
-    x1 = X - t + q2;
+    if constexpr (is_f64<T>::value) {
+        const double t = f64_mulmod(f64_renorm(x1.v, q.v, q2.v), w.w, w.ws, q.v);
+        const double X = x0.v;
+        x0.v = f64_add(X, t);
+        x1.v = f64_add(X, -t);
+    } else {
+        const T X = NOCSUB ? x0 : csub_min<T>(x0, q2);
+        const T t = mul_shoup_lazy<T>(x1, w.w, w.ws, q);
+        x0 = X + t;
+        x1 = X - t + q2;
+    }
 }
 template <typename T, bool NOCSUB> GP_HD void fwd_net4(T (&x)[4], const Tw3<T> &t, T q, T q2) {
+    if constexpr (is_f64<T>::value) {
+#pragma unroll
+        for (int j = 0; j < 4; j++) x[j].v = f64_renorm(x[j].v, q.v, q2.v);
+    }
     fwd_bfly<T, NOCSUB>(x[0], x[2], t.a, q, q2);
     fwd_bfly<T, NOCSUB>(x[1], x[3], t.a, q, q2);
     fwd_bfly<T, NOCSUB>(x[0], x[1], t.b0, q, q2);
     fwd_bfly<T, NOCSUB>(x[2], x[3], t.b1, q, q2);
 }
-template <typename T> GP_HD void inv_bfly(T &x0, T &x1, const TwPair<T> &w, T q, T q2) {
+template <typename T, bool RENORM = true> GP_HD void inv_bfly(T &x0, T &x1, const TwPair<T> &w, T q, T q2) {
     const T X = x0, Y = x1;
-    x0 = csub_min<T>(X + Y, q2);
-    x1 = mul_shoup_lazy<T>(X - Y + q2, w.w, w.ws, q);
+    if constexpr (is_f64<T>::value) {
+        const double sum = f64_add(X.v, Y.v);
+        x0.v = RENORM ? f64_renorm(sum, q.v, q2.v) : sum;
+        x1.v = f64_mulmod(f64_renorm(f64_add(X.v, -Y.v), q.v, q2.v), w.w, w.ws, q.v);
+    } else {
+        x0 = csub_min<T>(X + Y, q2);
+        x1 = mul_shoup_lazy<T>(X - Y + q2, w.w, w.ws, q);
+    }
 }
 template <typename T> GP_HD void inv_net4(T (&x)[4], const Tw3<T> &t, T q, T q2) {
-    inv_bfly<T>(x[0], x[1], t.b0, q, q2);
-    inv_bfly<T>(x[2], x[3], t.b1, q, q2);
-    inv_bfly<T>(x[0], x[2], t.a, q, q2);
-    inv_bfly<T>(x[1], x[3], t.a, q, q2);
+    inv_bfly<T, false>(x[0], x[1], t.b0, q, q2);
+    inv_bfly<T, false>(x[2], x[3], t.b1, q, q2);
+    inv_bfly<T, true>(x[0], x[2], t.a, q, q2);
+    inv_bfly<T, true>(x[1], x[3], t.a, q, q2);
 }
 
 // ---- passes over one block of B = 2^LOGB words -------------------------------------------------
@@ -368,16 +475,21 @@ GP_HD void f_last(const SmemView<T, LOGB> &sm, T *__restrict__ dst, const TwPair
             T x[4];
             sm.ld4(4 * g + ((g >> 4) << 2), x);
             fwd_net4<T, NOCSUB>(x, t[u], q, q2);
+            if constexpr (is_f64<T>::value) {
 #pragma unroll
-            for (int j = 0; j < 4; j++) {
-                T v = x[j];
-                if (NOCSUB) {
-                    // < (1 + 2*STAGES) q: one Shoup-by-one brings it to [0, 2q)
-                    v = reduce_lazy<T>(v, c.one_s, q);
-                } else {
-                    v = csub_min<T>(v, q2);
+                for (int j = 0; j < 4; j++) x[j].v = (double)f64_canonical(x[j].v, q.v, q2.v);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    T v = x[j];
+                    if (NOCSUB) {
+                        // < (1 + 2*STAGES) q: one Shoup-by-one brings it to [0, 2q)
+                        v = reduce_lazy<T>(v, c.one_s, q);
+                    } else {
+                        v = csub_min<T>(v, q2);
+                    }
+                    x[j] = csub_min<T>(v, q);
                 }
-                x[j] = csub_min<T>(v, q);
             }
             gst4(dst + 4 * g, x);
         }
@@ -471,7 +583,12 @@ GP_HD void i_last(const SmemView<T, LOGB> &sm, T *__restrict__ dst, const TwPair
         for (int j = 0; j < R; j++) x[j] = sm.ld(base + joff<LT0>(j));
         inv_net<T, R1, FINAL>(x, tw, nblk + sb, c);
 #pragma unroll
-        for (int j = 0; j < R; j++) dst[g + j * t0] = csub_min<T>(x[j], c.q);
+        for (int j = 0; j < R; j++) {
+            if constexpr (is_f64<T>::value)
+                reinterpret_cast<uint64_t *>(dst)[g + j * t0] = f64_canonical(x[j].v, c.q.v, c.q2.v);
+            else
+                dst[g + j * t0] = csub_min<T>(x[j], c.q);
+        }
     }
 }
 
@@ -543,8 +660,13 @@ GP_HD void fast_fwd_cta(uint32_t bid, void *smem, const T *src, T *dst, uint32_t
     const uint32_t sb = bid & ((1u << lsub) - 1), limb = (uint32_t)(pl % limbs);
     const size_t off = (pl << logn) + ((size_t)sb << LOGB);
     const LimbConst<T> c = lc[limb];
-    PlainSrc<T> s{src + off};
-    fast_fwd_block<T, LOGB, NOCSUB>(s, dst + off, smem, logn, sb, tw_all + ((size_t)limb << logn), c);
+    if constexpr (is_f64<T>::value) {
+        PlainSrc<T> s{src + off, 4 * (uint64_t)c.q.v};
+        fast_fwd_block<T, LOGB, NOCSUB>(s, dst + off, smem, logn, sb, tw_all + ((size_t)limb << logn), c);
+    } else {
+        PlainSrc<T> s{src + off};
+        fast_fwd_block<T, LOGB, NOCSUB>(s, dst + off, smem, logn, sb, tw_all + ((size_t)limb << logn), c);
+    }
 }
 template <typename T, int LOGB, bool NOCSUB>
 __global__ void __launch_bounds__(FastCfg<T, LOGB>::kThreads, FastCfg<T, LOGB>::kMinBlocks)
@@ -576,6 +698,13 @@ fast_ntt_inv_kernel(const T *src, T *dst, uint32_t limbs, uint32_t logn, const T
     fast_inv_cta<T, LOGB>(blockIdx.x, smem_raw, src, dst, limbs, logn, tw_all, lc);
 }
 
+// gadget digit as a double: any digit below 2^51 is already an exact, small enough multiplicand (the nets renormalise)
+struct F64DigitSrc {
+    const uint64_t *p;
+    uint32_t shift;
+    uint64_t mask;
+    GP_HD F64 operator()(uint32_t i) const { return F64{(double)((p[i] >> shift) & mask)}; }
+};
 // fused gadget decomposition + forward NTT (digit extraction is the load functor of pass 1);
 // geometry as decompose_cta in ntt.cuh, block = the whole transform (logn == LOGB)
 template <typename T, int LOGB, bool NOCSUB>
@@ -589,14 +718,25 @@ GP_HD void fast_decompose_cta(uint32_t bid, void *smem, const T *__restrict__ sr
     const uint32_t loc = (uint32_t)(orow % g.ell), t = loc / g.dpt, dg = loc % g.dpt;
     const LimbConst<T> c = lc[limb];
     const uint32_t sbits = lc[t].bits, shift = dg * g.base_bits;
-    T mask = 0;
-    if (shift < sbits) {
-        const uint32_t rem = sbits - shift, db = g.base_bits < rem ? g.base_bits : rem;
-        mask = db >= sizeof(T) * 8 ? ~(T)0 : (T)(((T)1 << db) - 1);
+    if constexpr (is_f64<T>::value) {
+        uint64_t mask = 0;
+        if (shift < sbits) {
+            const uint32_t rem = sbits - shift, db = g.base_bits < rem ? g.base_bits : rem;
+            mask = db >= 64 ? ~0ULL : ((1ULL << db) - 1);
+        }
+        const F64 *sp = src + (((row * g.src_cols + g.src_col0 + col) * g.limbs + t) << LOGB);
+        F64DigitSrc dsrc{reinterpret_cast<const uint64_t *>(sp), shift >= 64 ? 0u : shift, shift >= 64 ? 0ULL : mask};
+        fast_fwd_block<T, LOGB, NOCSUB>(dsrc, out + (pl << LOGB), smem, LOGB, 0, tw_all + ((size_t)limb << LOGB), c);
+    } else {
+        T mask = 0;
+        if (shift < sbits) {
+            const uint32_t rem = sbits - shift, db = g.base_bits < rem ? g.base_bits : rem;
+            mask = db >= sizeof(T) * 8 ? ~(T)0 : (T)(((T)1 << db) - 1);
+        }
+        const T *sp = src + (((row * g.src_cols + g.src_col0 + col) * g.limbs + t) << LOGB);
+        DigitSrc<T> dsrc{sp, shift >= sizeof(T) * 8 ? 0u : shift, shift >= sizeof(T) * 8 ? (T)0 : mask, c.q, c.one_s};
+        fast_fwd_block<T, LOGB, NOCSUB>(dsrc, out + (pl << LOGB), smem, LOGB, 0, tw_all + ((size_t)limb << LOGB), c);
     }
-    const T *sp = src + (((row * g.src_cols + g.src_col0 + col) * g.limbs + t) << LOGB);
-    DigitSrc<T> dsrc{sp, shift >= sizeof(T) * 8 ? 0u : shift, shift >= sizeof(T) * 8 ? (T)0 : mask, c.q, c.one_s};
-    fast_fwd_block<T, LOGB, NOCSUB>(dsrc, out + (pl << LOGB), smem, LOGB, 0, tw_all + ((size_t)limb << LOGB), c);
 }
 template <typename T, int LOGB, bool NOCSUB>
 __global__ void __launch_bounds__(FastCfg<T, LOGB>::kThreads, FastCfg<T, LOGB>::kMinBlocks)

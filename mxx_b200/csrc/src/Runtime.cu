@@ -52,6 +52,21 @@ void upload_tables(GpuContext *ctx) {
     chk(cudaMemcpy(d_fwd, t.fwd.data(), t.fwd.size() * sizeof(t.fwd[0]), cudaMemcpyHostToDevice));
     chk(cudaMemcpy(d_inv, t.inv.data(), t.inv.size() * sizeof(t.inv[0]), cudaMemcpyHostToDevice));
     chk(cudaMemcpy(d_lc, t.limb.data(), t.limb.size() * sizeof(t.limb[0]), cudaMemcpyHostToDevice));
+    if constexpr (sizeof(T) == 8) {
+        uint64_t qmax = 0;
+        for (uint64_t q : ctx->moduli) qmax = std::max(qmax, q);
+        const char *e = getenv("MXX_NTT_F64");
+        if (gp::host::f64_ok(qmax, true) && !(e && atoi(e) == 0) && !ctx->force_generic_ntt) {
+            const auto f = gp::host::f64_tables(t);
+            chk(cudaMalloc(&ctx->d_fwd_f64, f.fwd.size() * sizeof(f.fwd[0])));
+            chk(cudaMalloc(&ctx->d_inv_f64, f.inv.size() * sizeof(f.inv[0])));
+            chk(cudaMalloc(&ctx->d_limb_f64, f.limb.size() * sizeof(f.limb[0])));
+            chk(cudaMemcpy(ctx->d_fwd_f64, f.fwd.data(), f.fwd.size() * sizeof(f.fwd[0]), cudaMemcpyHostToDevice));
+            chk(cudaMemcpy(ctx->d_inv_f64, f.inv.data(), f.inv.size() * sizeof(f.inv[0]), cudaMemcpyHostToDevice));
+            chk(cudaMemcpy(ctx->d_limb_f64, f.limb.data(), f.limb.size() * sizeof(f.limb[0]), cudaMemcpyHostToDevice));
+            ctx->f64_ntt = true;
+        }
+    }
 }
 
 std::mutex g_live_mutex;
@@ -70,6 +85,9 @@ void free_context(GpuContext *ctx) {
     if (ctx->d_inv) cudaFree(ctx->d_inv);
     if (ctx->d_limb) cudaFree(ctx->d_limb);
     if (ctx->d_garner) cudaFree(ctx->d_garner);
+    if (ctx->d_fwd_f64) cudaFree(ctx->d_fwd_f64);
+    if (ctx->d_inv_f64) cudaFree(ctx->d_inv_f64);
+    if (ctx->d_limb_f64) cudaFree(ctx->d_limb_f64);
     for (int i = 0; i < 2; i++) {
         if (ctx->aux[i]) cudaStreamSynchronize(ctx->aux[i]);
         if (ctx->aux[i]) cudaStreamDestroy(ctx->aux[i]);

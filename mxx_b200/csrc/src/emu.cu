@@ -25,10 +25,15 @@
 namespace {
 using namespace gp;
 
+size_t g_f64_blocks = 0;  // blocks run through F64 kernels (tests assert the path was really taken)
+int g_f64 = 0;  // emu_set_f64: drive the FP64-pipe kernels (type F64) where the product library would
+
 template <typename T> struct Emu {
     int logn;
     uint32_t limbs;
     host::Tables<T> tab;
+    host::Tables<F64> ftab;
+    bool f64 = false;
     Emu(int logn_, uint32_t limbs_, const uint64_t *moduli) : logn(logn_), limbs(limbs_) {
         std::vector<uint64_t> m(moduli, moduli + limbs_), psi;
         for (uint64_t q : m) psi.push_back(host::primitive_2n_root(q, (uint64_t)1 << logn_));
@@ -36,11 +41,25 @@ template <typename T> struct Emu {
         uint64_t qmax = 0;
         for (uint64_t q : m) qmax = q > qmax ? q : qmax;
         nocsub = host::nocsub_ok(qmax, sizeof(T) == 8);
+        if constexpr (sizeof(T) == 8) {
+            if (g_f64 && host::f64_ok(qmax, true)) {
+                ftab = host::f64_tables(tab);
+                f64 = true;
+            }
+        }
     }
     // ---- compile-time-planned kernels (ntt_fast.cuh), same selection rule as MatrixNTT.inl ----
     bool fast_ok(int logb_cap) const { return logb_cap == 0 && fast_supported<T>(fast_block_log<T>(logn)); }
     template <int LOGB> void fast_fwd_blocks(std::vector<T> &d, size_t nbid, bool nocsub) {
         std::vector<uint32_t> sm(fast_smem_bytes<T, LOGB>() / 4 + 4);
+        if constexpr (sizeof(T) == 8) {
+            if (f64) {
+                g_f64_blocks += nbid;
+                for (size_t bid = 0; bid < nbid; bid++)
+                    fast_fwd_cta<F64, LOGB, false>((uint32_t)bid, sm.data(), (const F64 *)d.data(), (F64 *)d.data(), limbs, logn, ftab.fwd.data(), ftab.limb.data());
+                return;
+            }
+        }
         for (size_t bid = 0; bid < nbid; bid++) {
             if (nocsub) fast_fwd_cta<T, LOGB, true>((uint32_t)bid, sm.data(), d.data(), d.data(), limbs, logn, tab.fwd.data(), tab.limb.data());
             else fast_fwd_cta<T, LOGB, false>((uint32_t)bid, sm.data(), d.data(), d.data(), limbs, logn, tab.fwd.data(), tab.limb.data());
@@ -48,6 +67,14 @@ template <typename T> struct Emu {
     }
     template <int LOGB> void fast_inv_blocks(std::vector<T> &d, size_t nbid) {
         std::vector<uint32_t> sm(fast_smem_bytes<T, LOGB>() / 4 + 4);
+        if constexpr (sizeof(T) == 8) {
+            if (f64) {
+                g_f64_blocks += nbid;
+                for (size_t bid = 0; bid < nbid; bid++)
+                    fast_inv_cta<F64, LOGB>((uint32_t)bid, sm.data(), (const F64 *)d.data(), (F64 *)d.data(), limbs, logn, ftab.inv.data(), ftab.limb.data());
+                return;
+            }
+        }
         for (size_t bid = 0; bid < nbid; bid++)
             fast_inv_cta<T, LOGB>((uint32_t)bid, sm.data(), d.data(), d.data(), limbs, logn, tab.inv.data(), tab.limb.data());
     }
@@ -185,6 +212,13 @@ int do_decompose(int logn, uint32_t limbs, const uint64_t *moduli, const uint64_
 #define DEC_CASE(LB)                                                                                                          \
     case LB:                                                                                                                  \
         for (size_t bid = 0; bid < opl; bid++) {                                                                              \
+            if constexpr (sizeof(T) == 8) {                                                                                   \
+                if (e.f64) {                                                                                                  \
+                    g_f64_blocks++;                                                                                           \
+                    fast_decompose_cta<F64, LB, false>((uint32_t)bid, fsm.data(), (const F64 *)s.data(), (F64 *)o.data(), g, e.ftab.fwd.data(), e.ftab.limb.data()); \
+                    continue;                                                                                                 \
+                }                                                                                                             \
+            }                                                                                                                 \
             if (e.nocsub) fast_decompose_cta<T, LB, true>((uint32_t)bid, fsm.data(), s.data(), o.data(), g, e.tab.fwd.data(), e.tab.limb.data()); \
             else fast_decompose_cta<T, LB, false>((uint32_t)bid, fsm.data(), s.data(), o.data(), g, e.tab.fwd.data(), e.tab.limb.data());         \
         }                                                                                                                     \
@@ -369,6 +403,8 @@ int emu_sample_p1(int force_wide, int logn, uint32_t limbs, const uint64_t *modu
         return do_sample_p1<uint32_t>(logn, limbs, moduli, a, b, dm, tp2, d, cols, sigma, s, dgg, seed, out);
     } catch (...) { return 1; }
 }
+void emu_set_f64(int on) { g_f64 = on; }
+size_t emu_f64_blocks(void) { return g_f64_blocks; }
 // force_wide: 0 = the context rule (u32 words when all moduli < 2^30), 1 = u64 words regardless
 int emu_ntt(int force_wide, int logn, uint32_t limbs, const uint64_t *moduli, uint64_t *data, size_t polys, int inverse,
             int logb_cap) {

@@ -57,16 +57,21 @@ int launch_fast_decompose(GpuContext *ctx, const T *src, T *out, const gp::Decom
     constexpr size_t smem = gp::fast_smem_bytes<T, LOGB>();
     auto kernel = gp::fast_decompose_kernel<T, LOGB, NOCSUB>;
     if (optin_smem(kernel, smem, ctx->device, done)) return 1;
-    kernel<<<grid, gp::FastCfg<T, LOGB>::kThreads, smem, gp::cur(ctx)>>>(src, out, g, (const gp::TwPair<T> *)ctx->d_fwd,
-                                                                       (const gp::LimbConst<T> *)ctx->d_limb);
+    kernel<<<grid, gp::FastCfg<T, LOGB>::kThreads, smem, gp::cur(ctx)>>>(src, out, g, fwd_tab<T>(ctx), limb_tab<T>(ctx));
     gp::count_launch();
     GP_CHECK_LAUNCH("fast_decompose_kernel");
     return 0;
 }
 template <typename T> int dispatch_fast_decompose(GpuContext *ctx, const T *src, T *out, const gp::DecompGeom &g, unsigned grid, int logb) {
-#define GP_CALL(LB) (ctx->nocsub ? launch_fast_decompose<T, LB, true>(ctx, src, out, g, grid) : launch_fast_decompose<T, LB, false>(ctx, src, out, g, grid))
-    GP_FAST_LOGB_SWITCH(logb, GP_CALL)
+    if constexpr (gp::is_f64<T>::value) {
+#define GP_CALL(LB) launch_fast_decompose<T, LB, false>(ctx, src, out, g, grid)
+        GP_FAST_LOGB_SWITCH(logb, GP_CALL)
 #undef GP_CALL
+    } else {
+#define GP_CALL(LB) (ctx->nocsub ? launch_fast_decompose<T, LB, true>(ctx, src, out, g, grid) : launch_fast_decompose<T, LB, false>(ctx, src, out, g, grid))
+        GP_FAST_LOGB_SWITCH(logb, GP_CALL)
+#undef GP_CALL
+    }
 }
 
 // out (rows*ell x cols) <- digits of src[:, src_col0 : src_col0 + cols] (src in COEFF form)
@@ -85,7 +90,12 @@ int run_decompose(GpuContext *ctx, const T *src_coeff, T *out, size_t rows, size
     const size_t opl = rows * g.ell * cols * limbs;
     if (opl == 0) return 0;
     const int logn = ctx->logN, logb = ntt_block_log<T>(ctx), top = logn - logb;
-    if (to_eval && top == 0 && use_fast<T>(ctx, logb)) return dispatch_fast_decompose<T>(ctx, src_coeff, out, g, (unsigned)opl, logb);
+    if (to_eval && top == 0 && use_fast<T>(ctx, logb)) {
+        if constexpr (sizeof(T) == 8) {
+            if (ctx->f64_ntt) return dispatch_fast_decompose<gp::F64>(ctx, (const gp::F64 *)src_coeff, (gp::F64 *)out, g, (unsigned)opl, logb);
+        }
+        return dispatch_fast_decompose<T>(ctx, src_coeff, out, g, (unsigned)opl, logb);
+    }
     const size_t smem = gp::ntt_smem_bytes<T>(logb);
     if (ensure_ntt_smem<T>(ctx, smem)) return 1;
     const auto *tw = (const gp::TwPair<T> *)ctx->d_fwd;

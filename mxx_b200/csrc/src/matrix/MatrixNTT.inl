@@ -21,6 +21,17 @@ template <typename T> inline bool use_fast(const GpuContext *ctx, int logb) {
 }
 using gp::split_top;
 
+// device tables by working type: the F64 kernels have their own (Runtime.cu upload_tables)
+template <typename T> inline const gp::TwPair<T> *fwd_tab(const GpuContext *c) {
+    return (const gp::TwPair<T> *)(gp::is_f64<T>::value ? c->d_fwd_f64 : c->d_fwd);
+}
+template <typename T> inline const gp::TwPair<T> *inv_tab(const GpuContext *c) {
+    return (const gp::TwPair<T> *)(gp::is_f64<T>::value ? c->d_inv_f64 : c->d_inv);
+}
+template <typename T> inline const gp::LimbConst<T> *limb_tab(const GpuContext *c) {
+    return (const gp::LimbConst<T> *)(gp::is_f64<T>::value ? c->d_limb_f64 : c->d_limb);
+}
+
 // opt-in to > 48 KB of dynamic shared memory, once per kernel instantiation and device
 template <typename K> int optin_smem(K kernel, size_t bytes, int device, std::atomic<uint32_t> &done) {
     if (bytes <= 48 * 1024) return 0;
@@ -37,9 +48,8 @@ int launch_fast_fwd(GpuContext *ctx, const T *src, T *dst, unsigned grid, uint32
     constexpr size_t smem = gp::fast_smem_bytes<T, LOGB>();
     auto kernel = gp::fast_ntt_fwd_kernel<T, LOGB, NOCSUB>;
     if (optin_smem(kernel, smem, ctx->device, done)) return 1;
-    kernel<<<grid, gp::FastCfg<T, LOGB>::kThreads, smem, gp::cur(ctx)>>>(src, dst, limbs, (uint32_t)ctx->logN,
-                                                                       (const gp::TwPair<T> *)ctx->d_fwd,
-                                                                       (const gp::LimbConst<T> *)ctx->d_limb);
+    kernel<<<grid, gp::FastCfg<T, LOGB>::kThreads, smem, gp::cur(ctx)>>>(src, dst, limbs, (uint32_t)ctx->logN, fwd_tab<T>(ctx),
+                                                                       limb_tab<T>(ctx));
     gp::count_launch();
     GP_CHECK_LAUNCH("fast_ntt_fwd_kernel");
     return 0;
@@ -50,9 +60,8 @@ int launch_fast_inv(GpuContext *ctx, const T *src, T *dst, unsigned grid, uint32
     constexpr size_t smem = gp::fast_smem_bytes<T, LOGB>();
     auto kernel = gp::fast_ntt_inv_kernel<T, LOGB>;
     if (optin_smem(kernel, smem, ctx->device, done)) return 1;
-    kernel<<<grid, gp::FastCfg<T, LOGB>::kThreads, smem, gp::cur(ctx)>>>(src, dst, limbs, (uint32_t)ctx->logN,
-                                                                       (const gp::TwPair<T> *)ctx->d_inv,
-                                                                       (const gp::LimbConst<T> *)ctx->d_limb);
+    kernel<<<grid, gp::FastCfg<T, LOGB>::kThreads, smem, gp::cur(ctx)>>>(src, dst, limbs, (uint32_t)ctx->logN, inv_tab<T>(ctx),
+                                                                       limb_tab<T>(ctx));
     gp::count_launch();
     GP_CHECK_LAUNCH("fast_ntt_inv_kernel");
     return 0;
@@ -68,9 +77,15 @@ int launch_fast_inv(GpuContext *ctx, const T *src, T *dst, unsigned grid, uint32
         default: return gp::set_error("no compile-time NTT plan for this block size"); \
     }
 template <typename T> int dispatch_fast_fwd(GpuContext *ctx, const T *src, T *dst, unsigned grid, uint32_t limbs, int logb) {
-#define GP_CALL(LB) (ctx->nocsub ? launch_fast_fwd<T, LB, true>(ctx, src, dst, grid, limbs) : launch_fast_fwd<T, LB, false>(ctx, src, dst, grid, limbs))
-    GP_FAST_LOGB_SWITCH(logb, GP_CALL)
+    if constexpr (gp::is_f64<T>::value) {
+#define GP_CALL(LB) launch_fast_fwd<T, LB, false>(ctx, src, dst, grid, limbs)
+        GP_FAST_LOGB_SWITCH(logb, GP_CALL)
 #undef GP_CALL
+    } else {
+#define GP_CALL(LB) (ctx->nocsub ? launch_fast_fwd<T, LB, true>(ctx, src, dst, grid, limbs) : launch_fast_fwd<T, LB, false>(ctx, src, dst, grid, limbs))
+        GP_FAST_LOGB_SWITCH(logb, GP_CALL)
+#undef GP_CALL
+    }
 }
 template <typename T> int dispatch_fast_inv(GpuContext *ctx, const T *src, T *dst, unsigned grid, uint32_t limbs, int logb) {
 #define GP_CALL(LB) launch_fast_inv<T, LB>(ctx, src, dst, grid, limbs)
@@ -156,7 +171,12 @@ template <typename T> int run_ntt_fwd(GpuContext *ctx, const T *src, T *dst, siz
         }
     }
     const unsigned grid = (unsigned)(pl << top);
-    if (fast) return dispatch_fast_fwd<T>(ctx, src, dst, grid, limbs, logb);
+    if (fast) {
+        if constexpr (sizeof(T) == 8) {
+            if (ctx->f64_ntt) return dispatch_fast_fwd<gp::F64>(ctx, (const gp::F64 *)src, (gp::F64 *)dst, grid, limbs, logb);
+        }
+        return dispatch_fast_fwd<T>(ctx, src, dst, grid, limbs, logb);
+    }
     gp::ntt_fwd_kernel<T><<<grid, gp::NttCfg<T>::kThreads, smem, gp::cur(ctx)>>>(
         src, dst, limbs, (uint32_t)logn, (uint32_t)logb, (const gp::TwPair<T> *)ctx->d_fwd, (const gp::LimbConst<T> *)ctx->d_limb);
     gp::count_launch();
@@ -172,7 +192,11 @@ template <typename T> int run_ntt_inv(GpuContext *ctx, const T *src, T *dst, siz
     const size_t smem = gp::ntt_smem_bytes<T>(logb);
     const unsigned grid = (unsigned)(pl << top);
     if (fast) {
-        if (dispatch_fast_inv<T>(ctx, src, dst, grid, limbs, logb)) return 1;
+        bool f64 = false;
+        if constexpr (sizeof(T) == 8) f64 = ctx->f64_ntt;
+        if (f64) {
+            if (dispatch_fast_inv<gp::F64>(ctx, (const gp::F64 *)src, (gp::F64 *)dst, grid, limbs, logb)) return 1;
+        } else if (dispatch_fast_inv<T>(ctx, src, dst, grid, limbs, logb)) return 1;
     } else {
         if (ensure_ntt_smem<T>(ctx, smem)) return 1;
         gp::ntt_inv_kernel<T><<<grid, gp::NttCfg<T>::kThreads, smem, gp::cur(ctx)>>>(

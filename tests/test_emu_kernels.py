@@ -29,6 +29,9 @@ def emu():
     lib.emu_ntt.argtypes = [C.c_int, C.c_int, C.c_uint32, u64p, u64p, C.c_size_t, C.c_int, C.c_int]
     lib.emu_decompose.argtypes = [C.c_int, C.c_int, C.c_uint32, u64p, u64p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t,
                                   C.c_uint32, C.c_int, C.c_int, u64p, C.c_int]
+    lib.emu_set_f64.argtypes = [C.c_int]
+    lib.emu_set_f64.restype = None
+    lib.emu_f64_blocks.restype = C.c_size_t
     lib.emu_matmul.argtypes = [C.c_int, C.c_int, C.c_uint32, u64p, u64p, u64p, u64p] + [C.c_uint32] * 8 + [C.c_int]
     return lib
 
@@ -94,6 +97,77 @@ CASES = [
     (16384, 1, 24, 0, 1),   # u64 storage forced for a small modulus
     (16384, 1, 24, 14, 0),  # same ring through the generic kernel
 ]
+
+
+@pytest.fixture
+def emu_f64(emu):
+    """drive the FP64-pipe kernels (modarith.cuh F64) the library picks for u64 contexts with moduli < 2^51"""
+    emu.emu_set_f64(1)
+    before = emu.emu_f64_blocks()
+    yield emu
+    emu.emu_set_f64(0)
+    assert emu.emu_f64_blocks() > before, "the F64 kernels were not exercised"
+
+
+F64_CASES = [
+    # (n, depth, bits, force_wide)
+    (4096, 2, 51, 0),
+    (8192, 1, 51, 0),
+    (8192, 2, 40, 0),
+    (16384, 2, 51, 0),
+    (16384, 1, 31, 0),
+    (32768, 1, 51, 0),    # 2^13 blocks under an integer radix-4 global pass
+    (65536, 1, 51, 0),
+    (16384, 1, 24, 1),    # u64 storage forced for a small modulus
+]
+
+
+@pytest.mark.parametrize("n,depth,bits,fw", F64_CASES)
+def test_emu_f64_ntt_matches_oracle(emu_f64, n, depth, bits, fw):
+    pl = plan(n, depth, bits)
+    mod = np.array(pl.moduli, dtype=np.uint64)
+    assert int(mod.max()) < 1 << 51
+    a = pl.uniform(1, 3, seed=23 + n)
+    want = to_dev(pl.ntt(a))
+    d = a.copy()
+    assert emu_f64.emu_ntt(fw, n.bit_length() - 1, depth, p(mod), p(d), 3, 0, 0) == 0
+    assert np.array_equal(d, want)
+    assert emu_f64.emu_ntt(fw, n.bit_length() - 1, depth, p(mod), p(d), 3, 1, 0) == 0
+    assert np.array_equal(d, a)
+
+
+def test_emu_f64_ntt_extreme_values(emu_f64):
+    """all coefficients q-1 / 0 / alternating: the largest un-renormalised legs the FP64 butterflies see"""
+    for n, depth, bits in [(4096, 2, 51), (16384, 1, 51), (32768, 1, 51), (8192, 1, 33)]:
+        pl = plan(n, depth, bits)
+        mod = np.array(pl.moduli, dtype=np.uint64)
+        a = np.empty((1, 3, depth, n), dtype=np.uint64)
+        a[0, 0] = (mod - 1)[:, None]
+        a[0, 1] = 0
+        a[0, 2] = (mod - 1)[:, None]
+        a[0, 2, :, ::2] = 0
+        want = to_dev(pl.ntt(a))
+        d = a.copy()
+        assert emu_f64.emu_ntt(0, n.bit_length() - 1, depth, p(mod), p(d), 3, 0, 0) == 0
+        assert np.array_equal(d, want)
+        e = to_dev(a)
+        want_c = pl.intt(a)
+        assert emu_f64.emu_ntt(0, n.bit_length() - 1, depth, p(mod), p(e), 3, 1, 0) == 0
+        assert np.array_equal(e, want_c)
+
+
+@pytest.mark.parametrize("n,depth,bits,bb,small", [(4096, 1, 51, 17, 0), (8192, 2, 51, 13, 0), (4096, 2, 40, 20, 1)])
+def test_emu_f64_decompose_matches_oracle(emu_f64, n, depth, bits, bb, small):
+    pl = plan(n, depth, bits)
+    mod = np.array(pl.moduli, dtype=np.uint64)
+    rows, cols = 2, 3
+    src = pl.uniform(rows, cols, seed=5)
+    full = to_dev(pl.ntt(pl.decompose(src, bb, bool(small))))
+    ell = pl.ell(bb, bool(small))
+    for c0, w in [(0, cols), (1, 2)]:
+        out = np.zeros((rows * ell, w, depth, n), dtype=np.uint64)
+        assert emu_f64.emu_decompose(0, n.bit_length() - 1, depth, p(mod), p(src), rows, cols, c0, w, bb, small, 1, p(out), 0) == 0
+        assert np.array_equal(out, np.ascontiguousarray(full[:, c0:c0 + w]))
 
 
 @pytest.mark.parametrize("n,depth,bits,cap,fw", CASES)
