@@ -74,6 +74,7 @@ struct GpuContext {
     void *d_garner = nullptr;  // [L][L] u64: q_j^-1 mod q_i (compact wire format), built on first use
     std::mutex lazy_mutex;
     bool nocsub = false;             // forward NTT without conditional subtractions (36*qmax fits the word)
+    bool fuse_decompose_top = true;  // MXX_DECOMP_FUSE_TOP=0: separate digit kernel + first global pass (A/B)
     bool force_generic_ntt = false;  // MXX_NTT_GENERIC=1: use only the runtime-planned kernels of ntt.cuh
     int ntt_block_override = 0;      // MXX_NTT_BLOCK_LOG
     bool smem_configured = false;  // >48 KB dynamic shared memory opted in for the NTT kernels

@@ -9,6 +9,7 @@
 // twiddles and one Barrett reduction per lazily accumulated sum.
 #pragma once
 #include <stdint.h>
+#include <string.h>
 #include <cuda_runtime.h>
 
 // Block-level code is written against GP_TID / GP_NT / GP_SYNC so that the very same
@@ -141,13 +142,39 @@ GP_HD double f64_mulmod(double y, double w, double wq, double q) {
     const double c = fma(-b, q, h);
     return f64_add(c, l);
 }
-// signed lazy value -> canonical residue in [0, q) as an integer word
-GP_HD uint64_t f64_canonical(double x, double q, double qinv) {
+// Integer words <-> doubles without the slow 64-bit I2F/F2I conversions: for 0 <= u < 2^52 the double 2^52 + u has u
+// as its mantissa field, so one OR / AND plus one exact add converts either way.
+#define GP_F64_TWO52 4503599627370496.0
+#define GP_F64_TWO52_BITS 0x4330000000000000ULL
+GP_HD uint64_t f64_bits(double d) {
+#ifdef __CUDA_ARCH__
+    return (uint64_t)__double_as_longlong(d);
+#else
+    uint64_t u;
+    memcpy(&u, &d, 8);
+    return u;
+#endif
+}
+GP_HD double f64_from_bits(uint64_t u) {
+#ifdef __CUDA_ARCH__
+    return __longlong_as_double((long long)u);
+#else
+    double d;
+    memcpy(&d, &u, 8);
+    return d;
+#endif
+}
+GP_HD double f64_from_word(uint64_t u) { return f64_add(f64_from_bits(u | GP_F64_TWO52_BITS), -GP_F64_TWO52); }  // u < 2^52
+GP_HD uint64_t f64_to_word(double r) { return f64_bits(f64_add(r, GP_F64_TWO52)) & 0x000FFFFFFFFFFFFFULL; }     // 0 <= r < 2^52
+// signed lazy value -> canonical residue in [0, q), still a double
+GP_HD double f64_canonical_f(double x, double q, double qinv) {
     double r = f64_renorm(x, q, qinv);
     if (r < 0.0) r += q;
     if (r >= q) r -= q;
-    return (uint64_t)r;
+    return r;
 }
+// ... and as an integer word
+GP_HD uint64_t f64_canonical(double x, double q, double qinv) { return f64_to_word(f64_canonical_f(x, q, qinv)); }
 
 // Lazy accumulator for sum_k a_k*b_k mod q.
 template <typename T> struct Acc;

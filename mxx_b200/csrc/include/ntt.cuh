@@ -43,15 +43,16 @@ template <typename T> struct PlainSrc {
     GP_HD T operator()(uint32_t i) const { return p[i]; }
 };
 // F64 working type (modarith.cuh): the words in memory are u64 integers below 8q (canonical, or lazily reduced by
-// the integer global passes that precede the block kernel for rings above one CTA); one conditional subtraction
-// keeps the converted value below 2^53
+// the integer global passes that precede the block kernel for rings above one CTA); two conditional subtractions
+// bring the word below 2q < 2^52, where the mantissa trick converts it (modarith.cuh f64_from_word)
 template <> struct PlainSrc<F64> {
     const F64 *p;
     uint64_t q4;  // 4q
     GP_HD F64 operator()(uint32_t i) const {
         uint64_t r = reinterpret_cast<const uint64_t *>(p)[i];
         if (r >= q4) r -= q4;
-        return F64{(double)r};
+        if (r >= (q4 >> 1)) r -= q4 >> 1;
+        return F64{f64_from_word(r)};
     }
 };
 // Gadget digit of a coefficient-form residue, the fused load of decompose + NTT:
@@ -379,6 +380,56 @@ GP_HD void fwd_global_thread(size_t gid, T *data, uint32_t limbs, uint32_t logn,
     fwd_network<T, LOGR>(x, tw_all + ((size_t)limb << logn), (1u << (logn - lspan)) + b, c.q, c.q2);
 #pragma unroll
     for (int j = 0; j < R; j++) base[(size_t)j * stride] = x[j];  // lazy [0,4q): the next pass accepts it
+}
+// Gadget decomposition fused into the FIRST forward top pass (span n): the digits are extracted while the radix-R
+// groups are gathered, so the coefficient-form digit matrix is never written and re-read (rings above one CTA,
+// e.g. n = 2^15 with u64 words).  Geometry as decompose_cta; out receives what decompose_kernel<false> followed by
+// ntt_fwd_global_pass<LOGR>(lspan = logn) would leave.
+// One CTA covers 2^kDecompTopChunkLog (or all, for small rings) radix-R groups of ONE output (poly, limb), so the
+// digit geometry (a handful of 64-bit divisions) is worked out once per CTA and not per group.
+constexpr uint32_t kDecompTopChunkLog = 11;
+template <int LOGR> GP_HD uint32_t decompose_top_chunk_log(uint32_t logn) {
+    const uint32_t lg = logn - LOGR;
+    return lg < kDecompTopChunkLog ? lg : kDecompTopChunkLog;
+}
+template <typename T, int LOGR>
+GP_HD void decompose_fwd_global_cta(size_t bid, const T *__restrict__ src, T *__restrict__ out, const DecompGeom &g,
+                                    uint32_t logn, const TwPair<T> *__restrict__ tw_all,
+                                    const LimbConst<T> *__restrict__ lc) {
+    constexpr int R = 1 << LOGR;
+    const uint32_t lg = logn - LOGR, stride = 1u << lg, lchunk = decompose_top_chunk_log<LOGR>(logn);
+    const size_t pl = bid >> (lg - lchunk);  // out (poly, limb)
+    const uint32_t e0 = (uint32_t)(bid & ((1u << (lg - lchunk)) - 1)) << lchunk;
+    const uint32_t limb = (uint32_t)(pl % g.limbs);
+    const size_t opoly = pl / g.limbs;
+    const size_t orow = opoly / g.cols, col = opoly % g.cols;
+    const size_t row = orow / g.ell;
+    const uint32_t loc = (uint32_t)(orow % g.ell), t = loc / g.dpt, dg = loc % g.dpt;
+    const LimbConst<T> c = lc[limb];
+    const uint32_t sbits = lc[t].bits, shift = dg * g.base_bits;
+    T mask = 0;
+    if (shift < sbits) {
+        const uint32_t rem = sbits - shift, db = g.base_bits < rem ? g.base_bits : rem;
+        mask = db >= sizeof(T) * 8 ? ~(T)0 : (T)(((T)1 << db) - 1);
+    }
+    const T *sp = src + (((row * g.src_cols + g.src_col0 + col) * g.limbs + t) << logn) + e0;
+    DigitSrc<T> dsrc{sp, shift >= sizeof(T) * 8 ? 0u : shift, shift >= sizeof(T) * 8 ? (T)0 : mask, c.q, c.one_s};
+    const TwPair<T> *tw = tw_all + ((size_t)limb << logn);
+    T *base = out + (pl << logn) + e0;
+    for (uint32_t i = GP_TID; i < (1u << lchunk); i += GP_NT) {
+        T x[R];
+#pragma unroll
+        for (int j = 0; j < R; j++) x[j] = dsrc(i + (uint32_t)j * stride);
+        fwd_network<T, LOGR>(x, tw, 1u, c.q, c.q2);
+#pragma unroll
+        for (int j = 0; j < R; j++) base[i + (size_t)j * stride] = x[j];
+    }
+}
+template <typename T, int LOGR>
+__global__ void __launch_bounds__(256)
+decompose_fwd_global_pass(const T *__restrict__ src, T *__restrict__ out, DecompGeom g, uint32_t logn,
+                          const TwPair<T> *__restrict__ tw_all, const LimbConst<T> *__restrict__ lc) {
+    decompose_fwd_global_cta<T, LOGR>(blockIdx.x, src, out, g, logn, tw_all, lc);
 }
 template <typename T, int LOGR>
 __global__ void __launch_bounds__(256)

@@ -71,25 +71,7 @@ template <int LOGB> struct SmemView<uint64_t, LOGB> {
         *reinterpret_cast<uint4 *>(hi + i) = make_uint4((uint32_t)(x[0] >> 32), (uint32_t)(x[1] >> 32), (uint32_t)(x[2] >> 32), (uint32_t)(x[3] >> 32));
     }
 };
-// doubles travel through shared memory as their bit patterns in the u64 two-plane layout
-GP_HD uint64_t f64_bits(double d) {
-#ifdef __CUDA_ARCH__
-    return (uint64_t)__double_as_longlong(d);
-#else
-    uint64_t u;
-    memcpy(&u, &d, 8);
-    return u;
-#endif
-}
-GP_HD double f64_from_bits(uint64_t u) {
-#ifdef __CUDA_ARCH__
-    return __longlong_as_double((long long)u);
-#else
-    double d;
-    memcpy(&d, &u, 8);
-    return d;
-#endif
-}
+// doubles travel through shared memory as their bit patterns in the u64 two-plane layout (f64_bits, modarith.cuh)
 template <int LOGB> struct SmemView<F64, LOGB> {
     SmemView<uint64_t, LOGB> raw;
     GP_HD explicit SmemView(void *base) : raw(base) {}
@@ -189,12 +171,12 @@ GP_HD void gld4(const F64 *p, F64 (&x)[4]) {
     uint64_t u[4];
     gld4(reinterpret_cast<const uint64_t *>(p), u);
 #pragma unroll
-    for (int j = 0; j < 4; j++) x[j].v = (double)u[j];
+    for (int j = 0; j < 4; j++) x[j].v = f64_from_word(u[j]);
 }
 GP_HD void gst4(F64 *p, const F64 (&x)[4]) {  // x already canonical, see f_last
     uint64_t u[4];
 #pragma unroll
-    for (int j = 0; j < 4; j++) u[j] = (uint64_t)x[j].v;
+    for (int j = 0; j < 4; j++) u[j] = f64_to_word(x[j].v);
     gst4(reinterpret_cast<uint64_t *>(p), u);
 }
 
@@ -266,8 +248,9 @@ template <typename T, int LOGR, bool NOCSUB>
 GP_HD void fwd_net(T (&x)[1 << LOGR], const TwPair<T> *__restrict__ tw, uint32_t twbase, T q, T q2) {
     if constexpr (is_f64<T>::value) {
         static_assert(LOGR <= 5, "an F64 net may grow the unmultiplied leg for at most 5 stages");
+        // the first stage's multiplied legs (upper half) are renormalised by their butterflies
 #pragma unroll
-        for (int j = 0; j < (1 << LOGR); j++) x[j].v = f64_renorm(x[j].v, q.v, q2.v);
+        for (int j = 0; j < (1 << (LOGR - 1)); j++) x[j].v = f64_renorm(x[j].v, q.v, q2.v);
     }
     fwd_stage<T, LOGR, 0, NOCSUB>(x, tw, twbase, q, q2);
 }
@@ -360,7 +343,7 @@ template <typename T, bool NOCSUB> GP_HD void fwd_bfly(T &x0, T &x1, const TwPai
 template <typename T, bool NOCSUB> GP_HD void fwd_net4(T (&x)[4], const Tw3<T> &t, T q, T q2) {
     if constexpr (is_f64<T>::value) {
 #pragma unroll
-        for (int j = 0; j < 4; j++) x[j].v = f64_renorm(x[j].v, q.v, q2.v);
+        for (int j = 0; j < 2; j++) x[j].v = f64_renorm(x[j].v, q.v, q2.v);  // x[2], x[3]: by their butterflies
     }
     fwd_bfly<T, NOCSUB>(x[0], x[2], t.a, q, q2);
     fwd_bfly<T, NOCSUB>(x[1], x[3], t.a, q, q2);
@@ -477,7 +460,7 @@ GP_HD void f_last(const SmemView<T, LOGB> &sm, T *__restrict__ dst, const TwPair
             fwd_net4<T, NOCSUB>(x, t[u], q, q2);
             if constexpr (is_f64<T>::value) {
 #pragma unroll
-                for (int j = 0; j < 4; j++) x[j].v = (double)f64_canonical(x[j].v, q.v, q2.v);
+                for (int j = 0; j < 4; j++) x[j].v = f64_canonical_f(x[j].v, q.v, q2.v);
             } else {
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
@@ -703,7 +686,7 @@ struct F64DigitSrc {
     const uint64_t *p;
     uint32_t shift;
     uint64_t mask;
-    GP_HD F64 operator()(uint32_t i) const { return F64{(double)((p[i] >> shift) & mask)}; }
+    GP_HD F64 operator()(uint32_t i) const { return F64{f64_from_word((p[i] >> shift) & mask)}; }  // source words < 2^51
 };
 // fused gadget decomposition + forward NTT (digit extraction is the load functor of pass 1);
 // geometry as decompose_cta in ntt.cuh, block = the whole transform (logn == LOGB)

@@ -26,6 +26,7 @@ namespace {
 using namespace gp;
 
 size_t g_f64_blocks = 0;  // blocks run through F64 kernels (tests assert the path was really taken)
+int g_fuse_top = 1;  // emu_set_fuse_top: digits extracted inside the first global pass (the launcher's default)
 int g_f64 = 0;  // emu_set_f64: drive the FP64-pipe kernels (type F64) where the product library would
 
 template <typename T> struct Emu {
@@ -103,7 +104,7 @@ template <typename T> struct Emu {
         if (logb_cap > 0 && logb_cap < lb) lb = logb_cap;
         return lb;
     }
-    void fwd(std::vector<T> &d, size_t polys, int logb_cap) {
+    void fwd(std::vector<T> &d, size_t polys, int logb_cap, bool first_top_pass_done = false) {
         const int logb = block_log(logb_cap), top = logn - logb;
         const size_t pl = polys * limbs;
         std::vector<T> sm(ntt_smem_bytes<T>(logb) / sizeof(T) + 1);
@@ -112,7 +113,7 @@ template <typename T> struct Emu {
             split_top(top, passes, &np);
             uint32_t lspan = (uint32_t)logn;
             for (int i = 0; i < np; i++) {
-                const size_t total = pl << (logn - passes[i]);
+                const size_t total = (i == 0 && first_top_pass_done) ? 0 : pl << (logn - passes[i]);
                 for (size_t gid = 0; gid < total; gid++) switch (passes[i]) {
                         case 1: fwd_global_thread<T, 1>(gid, d.data(), limbs, logn, lspan, tab.fwd.data(), tab.limb.data()); break;
                         case 2: fwd_global_thread<T, 2>(gid, d.data(), limbs, logn, lspan, tab.fwd.data(), tab.limb.data()); break;
@@ -239,6 +240,25 @@ int do_decompose(int logn, uint32_t limbs, const uint64_t *moduli, const uint64_
     } else if (to_eval && top == 0) {
         for (size_t bid = 0; bid < opl; bid++)
             decompose_cta<T, true>((uint32_t)bid, sm.data(), s.data(), o.data(), g, logn, logb, e.tab.fwd.data(), e.tab.limb.data());
+    } else if (to_eval && g_fuse_top) {
+        // the launcher's fused digit extraction + first global pass (MatrixDecompose.inl run_decompose)
+        int passes[8], np = 0;
+        split_top(top, passes, &np);
+#define EMU_DFG(R)                                                                                                    \
+    case R: {                                                                                                         \
+        const size_t nb = opl << ((logn - R) - decompose_top_chunk_log<R>((uint32_t)logn));                            \
+        for (size_t bid = 0; bid < nb; bid++)                                                                         \
+            decompose_fwd_global_cta<T, R>(bid, s.data(), o.data(), g, (uint32_t)logn, e.tab.fwd.data(), e.tab.limb.data()); \
+    } break;
+        switch (passes[0]) {
+            EMU_DFG(1)
+            EMU_DFG(2)
+            EMU_DFG(3)
+            default:
+                EMU_DFG(4)
+        }
+#undef EMU_DFG
+        e.fwd(o, opolys, logb_cap, true);
     } else {
         for (size_t bid = 0; bid < (opl << top); bid++)
             decompose_cta<T, false>((uint32_t)bid, sm.data(), s.data(), o.data(), g, logn, logb, e.tab.fwd.data(), e.tab.limb.data());
@@ -404,6 +424,7 @@ int emu_sample_p1(int force_wide, int logn, uint32_t limbs, const uint64_t *modu
     } catch (...) { return 1; }
 }
 void emu_set_f64(int on) { g_f64 = on; }
+void emu_set_fuse_top(int on) { g_fuse_top = on; }
 size_t emu_f64_blocks(void) { return g_f64_blocks; }
 // force_wide: 0 = the context rule (u32 words when all moduli < 2^30), 1 = u64 words regardless
 int emu_ntt(int force_wide, int logn, uint32_t limbs, const uint64_t *moduli, uint64_t *data, size_t polys, int inverse,

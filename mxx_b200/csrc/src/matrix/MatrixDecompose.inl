@@ -107,6 +107,28 @@ int run_decompose(GpuContext *ctx, const T *src_coeff, T *out, size_t rows, size
         GP_CHECK_LAUNCH("decompose_kernel");
         return 0;
     }
+    if (to_eval && ctx->fuse_decompose_top) {
+        // rings above one CTA: the digits are extracted inside the first global pass of their forward transform
+        int passes[8], np = 0;
+        gp::split_top(top, passes, &np);
+        const unsigned gthreads = 256;
+        switch (passes[0]) {
+#define GP_DFG(R)                                                                                                    \
+    case R: {                                                                                                        \
+        const unsigned ggrid = (unsigned)(opl << ((logn - R) - gp::decompose_top_chunk_log<R>((uint32_t)logn)));     \
+        gp::decompose_fwd_global_pass<T, R><<<ggrid, gthreads, 0, gp::cur(ctx)>>>(src_coeff, out, g, (uint32_t)logn, tw, lc); \
+    } break;
+            GP_DFG(1)
+            GP_DFG(2)
+            GP_DFG(3)
+            default:
+                GP_DFG(4)
+#undef GP_DFG
+        }
+        gp::count_launch();
+        GP_CHECK_LAUNCH("decompose_fwd_global_pass");
+        return run_ntt_fwd<T>(ctx, out, out, rows * g.ell * cols, limbs, true);
+    }
     gp::decompose_kernel<T, false><<<grid, threads, 0, gp::cur(ctx)>>>(src_coeff, out, g, (uint32_t)logn, (uint32_t)logb, tw, lc);
     gp::count_launch();
     GP_CHECK_LAUNCH("decompose_kernel");

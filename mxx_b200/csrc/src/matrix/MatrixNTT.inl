@@ -150,8 +150,10 @@ int dispatch_inv_global(GpuContext *ctx, T *d, size_t pl, uint32_t limbs, uint32
     }
 }
 
-// dst = NTT(src) for `polys` polynomials of `limbs` limbs each (src may equal dst)
-template <typename T> int run_ntt_fwd(GpuContext *ctx, const T *src, T *dst, size_t polys, uint32_t limbs) {
+// dst = NTT(src) for `polys` polynomials of `limbs` limbs each (src may equal dst).
+// first_top_pass_done: the caller already ran the first global pass (fused with its producer, MatrixDecompose.inl).
+template <typename T>
+int run_ntt_fwd(GpuContext *ctx, const T *src, T *dst, size_t polys, uint32_t limbs, bool first_top_pass_done = false) {
     const size_t pl = polys * limbs;
     if (pl == 0) return 0;
     const int logn = ctx->logN, logb = ntt_block_log<T>(ctx), top = logn - logb;
@@ -166,7 +168,7 @@ template <typename T> int run_ntt_fwd(GpuContext *ctx, const T *src, T *dst, siz
         split_top(top, passes, &np);
         uint32_t lspan = (uint32_t)logn;
         for (int i = 0; i < np; i++) {
-            if (dispatch_fwd_global<T>(ctx, dst, pl, limbs, lspan, passes[i])) return 1;
+            if (!(i == 0 && first_top_pass_done) && dispatch_fwd_global<T>(ctx, dst, pl, limbs, lspan, passes[i])) return 1;
             lspan -= passes[i];
         }
     }

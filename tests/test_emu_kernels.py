@@ -31,6 +31,8 @@ def emu():
                                   C.c_uint32, C.c_int, C.c_int, u64p, C.c_int]
     lib.emu_set_f64.argtypes = [C.c_int]
     lib.emu_set_f64.restype = None
+    lib.emu_set_fuse_top.argtypes = [C.c_int]
+    lib.emu_set_fuse_top.restype = None
     lib.emu_f64_blocks.restype = C.c_size_t
     lib.emu_matmul.argtypes = [C.c_int, C.c_int, C.c_uint32, u64p, u64p, u64p, u64p] + [C.c_uint32] * 8 + [C.c_int]
     return lib
@@ -156,7 +158,7 @@ def test_emu_f64_ntt_extreme_values(emu_f64):
         assert np.array_equal(e, want_c)
 
 
-@pytest.mark.parametrize("n,depth,bits,bb,small", [(4096, 1, 51, 17, 0), (8192, 2, 51, 13, 0), (4096, 2, 40, 20, 1)])
+@pytest.mark.parametrize("n,depth,bits,bb,small", [(4096, 1, 51, 17, 0), (8192, 2, 51, 13, 0), (4096, 2, 40, 20, 1), (32768, 1, 51, 17, 0)])
 def test_emu_f64_decompose_matches_oracle(emu_f64, n, depth, bits, bb, small):
     pl = plan(n, depth, bits)
     mod = np.array(pl.moduli, dtype=np.uint64)
@@ -217,6 +219,13 @@ DEC_CASES = [
     (8192, 1, 28, 14, 0, 0),
     (4096, 1, 51, 17, 0, 0),
     (4096, 2, 24, 12, 1, 0),
+    # rings above one block: digits extracted inside the first global pass (radix 2 / 4 / 8 / 16)
+    (128, 2, 24, 8, 1, 6),
+    (256, 1, 51, 17, 0, 6),
+    (1024, 2, 24, 12, 0, 7),
+    (2048, 1, 28, 14, 0, 5),
+    (32768, 1, 51, 17, 0, 0),
+    (65536, 1, 28, 14, 1, 0),
 ]
 
 
@@ -237,6 +246,16 @@ def test_emu_decompose_matches_oracle(emu, n, depth, bits, bb, small, cap, to_ev
         st = emu.emu_decompose(0, n.bit_length() - 1, depth, p(mod), p(src), rows, cols, c0, w, bb, small, to_eval, p(out), cap)
         assert st == 0
         assert np.array_equal(out, np.ascontiguousarray(full[:, c0:c0 + w]))
+
+
+def test_emu_decompose_unfused_top_pass(emu):
+    """MXX_DECOMP_FUSE_TOP=0 path: digit kernel, then every global pass"""
+    emu.emu_set_fuse_top(0)
+    try:
+        test_emu_decompose_matches_oracle(emu, 512, 2, 28, 14, 0, 5, 1)
+        test_emu_decompose_matches_oracle(emu, 256, 1, 51, 17, 0, 6, 1)
+    finally:
+        emu.emu_set_fuse_top(1)
 
 
 MM_CASES = [

@@ -115,7 +115,7 @@ def test_add_sub_scalar_neg(mx, n, depth, bits, bb):
     assert not (gA == gB)
 
 
-@pytest.mark.parametrize("n,depth,bits,bb", PARAMS[:9])
+@pytest.mark.parametrize("n,depth,bits,bb", PARAMS[:9] + [PARAMS[10]])
 @pytest.mark.parametrize("small", [False, True])
 def test_decompose_matches_oracle_and_gadget_relation(mx, n, depth, bits, bb, small):
     params, plan = setup(mx, n, depth, bits, bb)
@@ -159,6 +159,8 @@ MD = [
     (16384, 3, 24, 12, 1, 1, 3),
     (16384, 2, 51, 17, 1, 1, 2),
     (32768, 1, 28, 14, 1, 1, 2),
+    (32768, 1, 51, 17, 1, 1, 2),   # u64 ring above one block: digits extracted inside the first global pass
+    (65536, 1, 28, 14, 1, 1, 1),
 ]
 
 

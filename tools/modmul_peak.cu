@@ -69,6 +69,40 @@ __global__ void __launch_bounds__(256) bfly_inv_kernel(T *out, T w, T ws, T q, i
     out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
 }
 
+// FP64-pipe butterflies (modarith.cuh f64_*; the kernels ntt_fast.cuh runs for u64 contexts with moduli < 2^51):
+// forward = renormalise the multiplied leg, multiply, add/subtract; inverse = add (renormalised every other stage),
+// subtract, renormalise, multiply
+template <bool INVERSE>
+__global__ void __launch_bounds__(256) bfly_f64_kernel(double *out, double w, double q, int rounds) {
+    double x[2 * kIlp];
+#pragma unroll
+    for (int i = 0; i < 2 * kIlp; i++) x[i] = (double)((threadIdx.x * 2654435761u + i * 40503u + blockIdx.x) % 1000003u);
+    const double qinv = 1.0 / q, wq = w / q;
+    for (int r = 0; r < rounds; r++) {
+#pragma unroll
+        for (int i = 0; i < kIlp; i++) {
+            const double X = x[2 * i], Y = x[2 * i + 1];
+            if (INVERSE) {
+                const double s = f64_add(X, Y);
+                x[2 * i] = (r & 1) ? f64_renorm(s, q, qinv) : s;
+                x[2 * i + 1] = f64_mulmod(f64_renorm(f64_add(X, -Y), q, qinv), w, wq, q);
+            } else {
+                const double t = f64_mulmod(f64_renorm(Y, q, qinv), w, wq, q);
+                x[2 * i] = f64_add(X, t);
+                x[2 * i + 1] = f64_add(X, -t);
+            }
+        }
+        if (!INVERSE && (r & 3) == 3) {  // the nets renormalise every value at entry (at most 5 stages apart)
+#pragma unroll
+            for (int i = 0; i < kIlp; i++) x[2 * i] = f64_renorm(x[2 * i], q, qinv);
+        }
+    }
+    double acc = 0;
+#pragma unroll
+    for (int i = 0; i < 2 * kIlp; i++) acc += x[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
+}
+
 // lazy multiply-accumulate chains (matmul inner loop): acc += a * b, fold every `fold` terms
 template <typename T>
 __global__ void __launch_bounds__(256) mac_kernel(T *out, LimbConst<T> c, int rounds, int fold) {
@@ -167,6 +201,10 @@ int main() {
     printf(", \"bfly_fwd_u64\": %.4e", bf / (t * 1e-3));
     t = time_ms([&] { bfly_inv_kernel<uint64_t><<<blocks, threads>>>((uint64_t *)out, w64, ws64, q64, kRounds); });
     printf(", \"bfly_inv_u64\": %.4e", bf / (t * 1e-3));
+    t = time_ms([&] { bfly_f64_kernel<false><<<blocks, threads>>>((double *)out, (double)w64, (double)q64, kRounds); });
+    printf(", \"bfly_fwd_f64\": %.4e", bf / (t * 1e-3));
+    t = time_ms([&] { bfly_f64_kernel<true><<<blocks, threads>>>((double *)out, (double)w64, (double)q64, kRounds); });
+    printf(", \"bfly_inv_f64\": %.4e", bf / (t * 1e-3));
     const LimbConst<uint32_t> c32 = limb_const<uint32_t>(q32);
     const LimbConst<uint64_t> c64 = limb_const<uint64_t>(q64);
     t = time_ms([&] { mac_kernel<uint32_t><<<blocks, threads>>>((uint32_t *)out, c32, kRounds, 16); });

@@ -16,7 +16,17 @@ using namespace gp;
 #ifndef LAB_LOGN
 #define LAB_LOGN 14
 #endif
+// LAB_WIDE: u64 words, integer kernels; LAB_F64: u64 words, FP64-pipe kernels (moduli < 2^51)
+#if defined(LAB_F64)
+typedef uint64_t T;
+typedef F64 K;
+#elif defined(LAB_WIDE)
+typedef uint64_t T;
+typedef uint64_t K;
+#else
 typedef uint32_t T;
+typedef uint32_t K;
+#endif
 
 static bool is_prime(uint64_t p) {
     if (p < 2) return false;
@@ -34,11 +44,13 @@ static bool is_prime(uint64_t p) {
         }                                                                          \
     } while (0)
 
-template <bool NOCSUB> static float run(const T *src, T *dst, unsigned grid, uint32_t limbs, const TwPair<T> *fwd, const TwPair<T> *inv,
-                                        const LimbConst<T> *lc, bool inverse, int reps) {
-    constexpr size_t smem = fast_smem_bytes<T, LAB_LOGN>();
-    auto kf = fast_ntt_fwd_kernel<T, LAB_LOGN, NOCSUB>;
-    auto ki = fast_ntt_inv_kernel<T, LAB_LOGN>;
+template <bool NOCSUB> static float run(const T *src_, T *dst_, unsigned grid, uint32_t limbs, const TwPair<K> *fwd, const TwPair<K> *inv,
+                                        const LimbConst<K> *lc, bool inverse, int reps) {
+    const K *src = (const K *)src_;
+    K *dst = (K *)dst_;
+    constexpr size_t smem = fast_smem_bytes<K, LAB_LOGN>();
+    auto kf = fast_ntt_fwd_kernel<K, LAB_LOGN, NOCSUB>;
+    auto ki = fast_ntt_inv_kernel<K, LAB_LOGN>;
     cudaFuncSetAttribute(kf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cudaFuncSetAttribute(ki, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cudaEvent_t e0, e1;
@@ -48,9 +60,9 @@ template <bool NOCSUB> static float run(const T *src, T *dst, unsigned grid, uin
     for (int r = 0; r < reps + 2; r++) {
         cudaEventRecord(e0);
         if (inverse)
-            ki<<<grid, FastCfg<T, LAB_LOGN>::kThreads, smem>>>(src, dst, limbs, LAB_LOGN, inv, lc);
+            ki<<<grid, FastCfg<K, LAB_LOGN>::kThreads, smem>>>(src, dst, limbs, LAB_LOGN, inv, lc);
         else
-            kf<<<grid, FastCfg<T, LAB_LOGN>::kThreads, smem>>>(src, dst, limbs, LAB_LOGN, fwd, lc);
+            kf<<<grid, FastCfg<K, LAB_LOGN>::kThreads, smem>>>(src, dst, limbs, LAB_LOGN, fwd, lc);
         cudaEventRecord(e1);
         cudaEventSynchronize(e1);
         float ms;
@@ -67,8 +79,13 @@ int main(int argc, char **argv) {
     for (uint64_t c = (((1ull << bits) - 2) / (2 * n)) * (2 * n) + 1; (int)moduli.size() < limbs && c > 2 * n; c -= 2 * n)
         if (is_prime(c)) moduli.push_back(c);
     for (uint64_t q : moduli) psi.push_back(host::primitive_2n_root(q, n));
-    const host::Tables<T> t = host::build_tables<T>(LAB_LOGN, moduli, psi);
-    const bool nocsub = host::nocsub_ok(moduli[0], false);
+#if defined(LAB_F64)
+    const host::Tables<K> t = host::f64_tables(host::build_tables<T>(LAB_LOGN, moduli, psi));
+    const bool nocsub = false;
+#else
+    const host::Tables<K> t = host::build_tables<T>(LAB_LOGN, moduli, psi);
+    const bool nocsub = host::nocsub_ok(moduli[0], sizeof(T) == 8);
+#endif
     const size_t words = (size_t)polys * limbs * n;
     std::vector<T> h(words);
     uint64_t s = 0x9E3779B97F4A7C15ull;
@@ -77,18 +94,18 @@ int main(int argc, char **argv) {
         h[i] = (T)(s % moduli[(i >> LAB_LOGN) % limbs]);
     }
     T *d_a, *d_b, *d_c;
-    TwPair<T> *d_f, *d_i;
-    LimbConst<T> *d_l;
+    TwPair<K> *d_f, *d_i;
+    LimbConst<K> *d_l;
     CK(cudaMalloc(&d_a, words * sizeof(T)));
     CK(cudaMalloc(&d_b, words * sizeof(T)));
     CK(cudaMalloc(&d_c, words * sizeof(T)));
-    CK(cudaMalloc(&d_f, t.fwd.size() * sizeof(TwPair<T>)));
-    CK(cudaMalloc(&d_i, t.inv.size() * sizeof(TwPair<T>)));
-    CK(cudaMalloc(&d_l, t.limb.size() * sizeof(LimbConst<T>)));
+    CK(cudaMalloc(&d_f, t.fwd.size() * sizeof(TwPair<K>)));
+    CK(cudaMalloc(&d_i, t.inv.size() * sizeof(TwPair<K>)));
+    CK(cudaMalloc(&d_l, t.limb.size() * sizeof(LimbConst<K>)));
     CK(cudaMemcpy(d_a, h.data(), words * sizeof(T), cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(d_f, t.fwd.data(), t.fwd.size() * sizeof(TwPair<T>), cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(d_i, t.inv.data(), t.inv.size() * sizeof(TwPair<T>), cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(d_l, t.limb.data(), t.limb.size() * sizeof(LimbConst<T>), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(d_f, t.fwd.data(), t.fwd.size() * sizeof(TwPair<K>), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(d_i, t.inv.data(), t.inv.size() * sizeof(TwPair<K>), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(d_l, t.limb.data(), t.limb.size() * sizeof(LimbConst<K>), cudaMemcpyHostToDevice));
     const unsigned grid = (unsigned)((size_t)polys * limbs);
     const float f = nocsub ? run<true>(d_a, d_b, grid, limbs, d_f, d_i, d_l, false, 5) : run<false>(d_a, d_b, grid, limbs, d_f, d_i, d_l, false, 5);
     const float iv = run<false>(d_b, d_c, grid, limbs, d_f, d_i, d_l, true, 5);

@@ -54,6 +54,27 @@ def md(reps=REPS):
     return out
 
 
+def c4(reps=REPS):
+    """one C4 gate's fused mul_decompose: (2 x 24) * G^-1(1 x 24) at n = 2^15, L = 8 x 51-bit, base 2^17"""
+    n, depth, bits, bb = 1 << 15, 8, 51, 17
+    moduli = standard_moduli(n, depth, bits)
+    params = GpuDCRTPolyParams(n, moduli, bb)
+    ell = params.modulus_digits()
+    S = np.empty((2, ell, depth, n), dtype=np.uint64)
+    O = np.empty((1, ell, depth, n), dtype=np.uint64)
+    uniform_host(S, moduli, 2)
+    uniform_host(O, moduli, 3)
+    gS, gO = GpuDCRTPolyMatrix.from_rns(params, S), GpuDCRTPolyMatrix.from_rns(params, O)
+    t = params.timer()
+    for _ in range(reps):
+        t.start()
+        out = gS.mul_decompose(gO, fused=True)
+        t.stop()
+        ms = t.elapsed_ms()
+    print(f"mul_decompose C4 gate fused: {ms:.3f} ms")
+    return out
+
+
 def mul(reps=REPS):
     n, depth, bits = 1 << 14, 15, 24
     moduli = standard_moduli(n, depth, bits)
@@ -89,6 +110,8 @@ if __name__ == "__main__":
         ntt(1 << 16, 8, 28, 128)
     if what in ("md", "all"):
         md()
+    if what in ("c4",):
+        c4()
     if what in ("mul", "all"):
         mul()
     ffi.device_synchronize()
