@@ -262,4 +262,97 @@ matmul_kernel(T *__restrict__ out, const T *__restrict__ A, const T *__restrict_
     matmul_thread<T, V, TR, TC, UNROLL>(blockIdx.x, blockIdx.y, blockIdx.z, threadIdx.x, blockDim.x, out, A, B, g, lc);
 }
 
+// ---- the same product on the FP64 pipe (u64 words, every modulus below 2^51; modarith.cuh f64_*) --------------
+// A 64-bit lazy MAC is a 128-bit multiply-add (measured 0.78e12 MAC/s); on exact doubles a term costs 7 FP64
+// operations: b/q is estimated as b * (1/q) (one DMUL per loaded B word, relative error 2^-52, so the rounded quotient
+// of a*b is within 1 of the true one and the reduced term |a*b - k q| <= q), then f64_mulmod's exact h/l split.
+// The accumulator is an integer-valued double: q/2 + fold*q < 2^53 terms between renormalisations
+// (fold = f64_mac_fold_terms, 3 for 51-bit moduli).  Operands are canonical residues (what every kernel stores);
+// the result is the canonical residue, bit-identical with matmul_kernel<uint64_t>.
+template <int V, int TR, int TC, int UNROLL = 2>
+GP_HD void matmul_f64_thread(uint32_t bx, uint32_t by, uint32_t bz, uint32_t tid, uint32_t ntid, uint64_t *__restrict__ out,
+                             const uint64_t *__restrict__ A, const uint64_t *__restrict__ B, const MatmulGeom &g,
+                             const LimbConst<F64> *__restrict__ lc) {
+    typedef uint64_t T;
+    const uint32_t rows = g.rows, inner = g.inner, cols = g.cols, limbs = g.limbs, logn = g.logn, fold = g.fold;
+    const uint32_t chunks = ((1u << logn) / V + ntid - 1) / ntid;
+    const uint32_t limb = bx / chunks, chunk = bx % chunks;
+    const uint32_t slot = (chunk * ntid + tid) * V;
+    if (slot >= (1u << logn)) return;
+    const size_t poly_words = (size_t)limbs << logn;
+    const size_t in_poly = ((size_t)limb << logn) + slot;
+    const uint32_t r0 = bz * TR, c0 = by * TC;
+    const double q = lc[limb].q.v, qinv = lc[limb].q2.v;  // LimbConst<F64>::q2 carries 1/q (host_tables.hpp)
+
+    double acc[TR][TC][V];
+#pragma unroll
+    for (int i = 0; i < TR; i++)
+#pragma unroll
+        for (int j = 0; j < TC; j++)
+#pragma unroll
+            for (int v = 0; v < V; v++) acc[i][j][v] = 0.0;
+
+    size_t arow[TR], bcol[TC];
+#pragma unroll
+    for (int i = 0; i < TR; i++) arow[i] = (size_t)(r0 + i < rows ? r0 + i : rows - 1) * inner * poly_words + in_poly;
+#pragma unroll
+    for (int j = 0; j < TC; j++) bcol[j] = (size_t)(g.b_col0 + (c0 + j < cols ? c0 + j : cols - 1)) * poly_words + in_poly;
+    const size_t bstep = (size_t)g.b_cols * poly_words;
+
+    uint32_t since = 0;
+    constexpr int kUnroll = UNROLL;
+#pragma unroll kUnroll
+    for (uint32_t k = 0; k < inner; k++) {
+        Vec<T, V> a[TR], b[TC];
+#pragma unroll
+        for (int i = 0; i < TR; i++) a[i] = ldv<T, V>(A + arow[i] + (size_t)k * poly_words);
+#pragma unroll
+        for (int j = 0; j < TC; j++) b[j] = ldv_stream<T, V>(B + bcol[j] + (size_t)k * bstep);
+        double af[TR][V], bf[TC][V], bq[TC][V];
+#pragma unroll
+        for (int i = 0; i < TR; i++)
+#pragma unroll
+            for (int v = 0; v < V; v++) af[i][v] = f64_from_word(a[i].v[v]);
+#pragma unroll
+        for (int j = 0; j < TC; j++)
+#pragma unroll
+            for (int v = 0; v < V; v++) {
+                bf[j][v] = f64_from_word(b[j].v[v]);
+                bq[j][v] = f64_mul(bf[j][v], qinv);
+            }
+#pragma unroll
+        for (int i = 0; i < TR; i++)
+#pragma unroll
+            for (int j = 0; j < TC; j++)
+#pragma unroll
+                for (int v = 0; v < V; v++) acc[i][j][v] = f64_add(acc[i][j][v], f64_mulmod(af[i][v], bf[j][v], bq[j][v], q));
+        if (++since == fold) {
+            since = 0;
+#pragma unroll
+            for (int i = 0; i < TR; i++)
+#pragma unroll
+                for (int j = 0; j < TC; j++)
+#pragma unroll
+                    for (int v = 0; v < V; v++) acc[i][j][v] = f64_renorm(acc[i][j][v], q, qinv);
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < TR; i++)
+#pragma unroll
+        for (int j = 0; j < TC; j++) {
+            if (r0 + i < rows && c0 + j < cols) {
+                Vec<T, V> o;
+#pragma unroll
+                for (int v = 0; v < V; v++) o.v[v] = f64_canonical(acc[i][j][v], q, qinv);
+                stv_stream<T, V>(out + ((size_t)(r0 + i) * g.out_cols + g.out_col0 + c0 + j) * poly_words + in_poly, o);
+            }
+        }
+}
+template <int V, int TR, int TC, int UNROLL = 2, int NT = 128>
+__global__ void __launch_bounds__(NT)
+matmul_f64_kernel(uint64_t *__restrict__ out, const uint64_t *__restrict__ A, const uint64_t *__restrict__ B, MatmulGeom g,
+                  const LimbConst<F64> *__restrict__ lc) {
+    matmul_f64_thread<V, TR, TC, UNROLL>(blockIdx.x, blockIdx.y, blockIdx.z, threadIdx.x, blockDim.x, out, A, B, g, lc);
+}
+
 }  // namespace gp

@@ -78,6 +78,8 @@ struct GpuContext {
     bool force_generic_ntt = false;  // MXX_NTT_GENERIC=1: use only the runtime-planned kernels of ntt.cuh
     int ntt_block_override = 0;      // MXX_NTT_BLOCK_LOG
     bool smem_configured = false;  // >48 KB dynamic shared memory opted in for the NTT kernels
+    bool f64_matmul = true;      // MXX_MATMUL_F64=0: keep the 128-bit integer MAC in FP64-pipe contexts (A/B)
+    uint32_t f64_mac_fold = 1;   // reduced terms between renormalisations of the FP64 accumulator
     uint32_t mac_fold = 1;   // products that fit one lazy accumulator between folds
     // chunked host->device load pipeline (MatrixHostLoad.inl), built on first use
     void *load_pipe = nullptr;

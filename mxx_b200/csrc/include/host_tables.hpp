@@ -151,6 +151,13 @@ inline Tables<F64> f64_tables(const Tables<uint64_t> &t) {
 inline bool f64_ok(uint64_t qmax, bool wide) { return wide && qmax < ((uint64_t)1 << 51); }
 
 // products that fit one lazy accumulator (2^64 for u32 words, 2^128 for u64) on top of a folded residue
+// FP64 product (arith.cuh matmul_f64_thread): reduced terms of magnitude <= q on top of a renormalised
+// accumulator (<= q/2, plus the rounding slack of the quotient estimate) must stay below 2^53
+inline uint32_t f64_mac_fold_terms(uint64_t qmax) {
+    const long double room = 9007199254740992.0L / (long double)qmax - 0.51L;
+    uint64_t t = room < 1.0L ? 1 : (uint64_t)room;
+    return (uint32_t)(t > 4096 ? 4096 : t);
+}
 inline uint32_t mac_fold_terms(uint64_t qmax, bool wide) {
     const u128 q2 = (u128)(qmax - 1) * (qmax - 1);
     const u128 room = wide ? (~(u128)0 - qmax) : ((u128)~0ull - qmax);

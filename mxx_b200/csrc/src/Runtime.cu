@@ -160,6 +160,8 @@ int gpu_context_create(uint32_t logN, uint32_t L, uint32_t dnum, const uint64_t 
         ctx->crt_bits = 64 - (uint32_t)__builtin_clzll(qmax);
         ctx->wide = needs_wide(qmax);
         ctx->mac_fold = mac_fold_terms(qmax, ctx->wide);
+        ctx->f64_mac_fold = f64_mac_fold_terms(qmax);
+        if (const char *env = getenv("MXX_MATMUL_F64")) ctx->f64_matmul = env[0] != '0';
         ctx->nocsub = nocsub_ok(qmax, ctx->wide);
         if (const char *env = getenv("MXX_NTT_GENERIC")) ctx->force_generic_ntt = env[0] == '1';
         if (const char *env = getenv("MXX_DECOMP_FUSE_TOP")) ctx->fuse_decompose_top = env[0] != '0';

@@ -280,6 +280,18 @@ void matmul_grid(std::vector<T> &out, const std::vector<T> &A, const std::vector
                     matmul_thread<T, V, TR, TC>(bx, by, bz, t, threads, out.data(), A.data(), B.data(), g, lc);
 }
 
+template <int V, int TR, int TC>
+void matmul_f64_grid(std::vector<uint64_t> &out, const std::vector<uint64_t> &A, const std::vector<uint64_t> &B, const MatmulGeom &g,
+                     const LimbConst<F64> *lc) {
+    const uint32_t threads = 4;
+    const uint32_t per_limb = ((1u << g.logn) / V + threads - 1) / threads;
+    for (uint32_t bz = 0; bz < (g.rows + TR - 1) / TR; bz++)
+        for (uint32_t by = 0; by < (g.cols + TC - 1) / TC; by++)
+            for (uint32_t bx = 0; bx < g.limbs * per_limb; bx++)
+                for (uint32_t t = 0; t < threads; t++)
+                    matmul_f64_thread<V, TR, TC>(bx, by, bz, t, threads, out.data(), A.data(), B.data(), g, lc);
+}
+
 template <typename T>
 int do_matmul(int logn, uint32_t limbs, const uint64_t *moduli, uint64_t *out, const uint64_t *A, const uint64_t *B,
               uint32_t rows, uint32_t inner, uint32_t cols, uint32_t b_cols, uint32_t b_col0, uint32_t out_cols,
@@ -295,6 +307,20 @@ int do_matmul(int logn, uint32_t limbs, const uint64_t *moduli, uint64_t *out, c
     auto a = narrow<T>(A, (size_t)rows * inner * pw), b = narrow<T>(B, (size_t)inner * b_cols * pw);
     auto o = narrow<T>(out, (size_t)rows * out_cols * pw);
     constexpr int VMAX = 16 / (int)sizeof(T);
+    if constexpr (sizeof(T) == 8) {
+        if (e.f64) {  // the FP64-pipe product the launcher picks for these contexts (MatrixArith.inl run_matmul)
+            g.fold = fold ? fold : host::f64_mac_fold_terms(qmax);
+            g_f64_blocks++;
+            switch (variant) {
+                case 0: matmul_f64_grid<VMAX, 1, 6>(o, a, b, g, e.ftab.limb.data()); break;
+                case 1: matmul_f64_grid<VMAX, 2, 4>(o, a, b, g, e.ftab.limb.data()); break;
+                case 2: matmul_f64_grid<VMAX / 2, 4, 4>(o, a, b, g, e.ftab.limb.data()); break;
+                default: matmul_f64_grid<VMAX, 1, 1>(o, a, b, g, e.ftab.limb.data()); break;
+            }
+            widen(o, out);
+            return 0;
+        }
+    }
     switch (variant) {
         case 0: matmul_grid<T, VMAX, 1, 4>(o, a, b, g, e.tab.limb.data()); break;
         case 1: matmul_grid<T, VMAX, 2, 4>(o, a, b, g, e.tab.limb.data()); break;

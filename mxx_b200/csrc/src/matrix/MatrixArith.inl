@@ -34,6 +34,17 @@ int launch_matmul_tile(GpuContext *ctx, T *out, const T *A, const T *B, const gp
     return 0;
 }
 
+template <int V, int TR, int TC, int UNROLL = 2, int NT = 128>
+int launch_matmul_f64_tile(GpuContext *ctx, uint64_t *out, const uint64_t *A, const uint64_t *B, const gp::MatmulGeom &g) {
+    const unsigned threads = NT;
+    const unsigned per_limb = (unsigned)(((size_t)ctx->N / V + threads - 1) / threads);
+    dim3 grid(g.limbs * per_limb, (g.cols + TC - 1) / TC, (g.rows + TR - 1) / TR);
+    gp::matmul_f64_kernel<V, TR, TC, UNROLL, NT><<<grid, threads, 0, gp::cur(ctx)>>>(out, A, B, g, (const gp::LimbConst<gp::F64> *)ctx->d_limb_f64);
+    gp::count_launch();
+    GP_CHECK_LAUNCH("matmul_f64_kernel");
+    return 0;
+}
+
 // out[:, out_col0 : out_col0+cols] = A(rows x inner) * B[:, b_col0 : b_col0+cols]
 template <typename T> int run_matmul(GpuContext *ctx, T *out, const T *A, const T *B, gp::MatmulGeom g) {
     if (g.rows == 0 || g.cols == 0 || g.limbs == 0) return 0;
@@ -49,6 +60,15 @@ template <typename T> int run_matmul(GpuContext *ctx, T *out, const T *A, const 
         return 0;
     }
     if (V != VMAX) return launch_matmul_tile<T, 1, 1, 1>(ctx, out, A, B, g);  // tiny rings (n < 16 bytes of words)
+    if constexpr (sizeof(T) == 8) {
+        if (ctx->f64_ntt && ctx->f64_matmul) {  // moduli < 2^51: the product on the FP64 pipe (arith.cuh)
+            g.fold = ctx->f64_mac_fold;
+            if (g.rows >= 4) return launch_matmul_f64_tile<VMAX / 2, 4, 4>(ctx, out, A, B, g);
+            if (g.rows >= 2) return launch_matmul_f64_tile<VMAX, 2, 4>(ctx, out, A, B, g);
+            if (g.cols % 6 == 0) return launch_matmul_f64_tile<VMAX, 1, 6, 2, 64>(ctx, out, A, B, g);
+            return launch_matmul_f64_tile<VMAX, 1, 1, 6, 128>(ctx, out, A, B, g);
+        }
+    }
     // Register tile: the wider the tile the fewer operand loads per product.  rows == 1 (the
     // BGG / bench_matrix_mul shape) streams B once and re-reads A from L2.
     if (g.rows >= 4) return launch_matmul_tile<T, VMAX / 2, 4, 4>(ctx, out, A, B, g);

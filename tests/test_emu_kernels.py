@@ -291,6 +291,41 @@ def test_emu_matmul_matches_oracle(emu, n, depth, bits, r, k, c, variant, fold):
         assert np.all(wide[:, :2] == 7) and np.all(wide[:, c + 1:] == 7)
 
 
+F64_MM_CASES = [
+    # (n, depth, bits, r, k, c, variant, fold)
+    (16, 2, 51, 1, 30, 6, 0, 0),
+    (16, 2, 51, 1, 5, 7, 0, 0),
+    (16, 2, 51, 3, 21, 5, 1, 0),
+    (16, 2, 51, 5, 9, 6, 2, 0),
+    (16, 2, 40, 2, 40, 3, 1, 0),    # smaller moduli: more terms between renormalisations
+    (16, 1, 31, 1, 70, 4, 3, 0),
+    (16, 2, 51, 2, 24, 4, 1, 1),    # renormalise after every term
+]
+
+
+@pytest.mark.parametrize("n,depth,bits,r,k,c,variant,fold", F64_MM_CASES)
+def test_emu_f64_matmul_matches_oracle(emu_f64, n, depth, bits, r, k, c, variant, fold):
+    test_emu_matmul_matches_oracle(emu_f64, n, depth, bits, r, k, c, variant, fold)
+
+
+def test_emu_f64_matmul_worst_case_accumulation(emu_f64):
+    """every operand q-1 / mixed 0, 1, q-1: the largest terms and quotient-estimate errors of the FP64 product"""
+    for bits, n in [(51, 16), (50, 16), (33, 16)]:
+        pl = plan(n, 1, bits)
+        q = pl.moduli[0]
+        mod = np.array(pl.moduli, dtype=np.uint64)
+        k = 70
+        A = np.full((2, k, 1, n), q - 1, dtype=np.uint64)
+        B = np.full((k, 4, 1, n), q - 1, dtype=np.uint64)
+        rng = np.random.default_rng(bits)
+        A[1] = rng.choice(np.array([0, 1, q - 1, q // 2, q // 2 + 1], dtype=np.uint64), size=(k, 1, n))
+        B[:, 1] = rng.choice(np.array([0, 1, q - 1, q // 2, q // 2 + 1], dtype=np.uint64), size=(k, 1, n))
+        want = pl.mul(A, B)
+        out = np.zeros_like(want)
+        assert emu_f64.emu_matmul(0, n.bit_length() - 1, 1, p(mod), p(out), p(A), p(B), 2, k, 4, 4, 0, 4, 0, 0, 1) == 0
+        assert np.array_equal(out, want)
+
+
 def test_emu_matmul_worst_case_accumulation(emu):
     """every operand q-1: the largest lazily accumulated sums"""
     for bits, n in [(29, 16), (61, 16), (24, 16)]:
