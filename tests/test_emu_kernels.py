@@ -138,6 +138,29 @@ def test_emu_f64_ntt_matches_oracle(emu_f64, n, depth, bits, fw):
     assert np.array_equal(d, a)
 
 
+def test_emu_f64_mixed_modulus_sizes(emu_f64):
+    """a wide context mixing 20-, 35- and 51-bit limbs: per-limb 1/q, fold count from the largest modulus"""
+    n = 4096
+    moduli = orc.prime_chain(n, 20, 1) + orc.prime_chain(n, 51, 1) + orc.prime_chain(n, 35, 1)
+    pl = orc.Plan(n, moduli)
+    mod = np.array(moduli, dtype=np.uint64)
+    a = pl.uniform(1, 2, seed=77)
+    a[0, 1] = (mod - 1)[:, None]
+    d = a.copy()
+    assert emu_f64.emu_ntt(0, 12, 3, p(mod), p(d), 2, 0, 0) == 0
+    assert np.array_equal(d, to_dev(pl.ntt(a)))
+    assert emu_f64.emu_ntt(0, 12, 3, p(mod), p(d), 2, 1, 0) == 0
+    assert np.array_equal(d, a)
+    pl16 = orc.Plan(16, [orc.prime_chain(16, b, 1)[0] for b in (20, 51, 35)])
+    mod16 = np.array(pl16.moduli, dtype=np.uint64)
+    A, B = pl16.uniform(2, 9, seed=1), pl16.uniform(9, 4, seed=2)
+    A[1] = (mod16 - 1)[:, None]
+    want = pl16.mul(A, B)
+    out = np.zeros_like(want)
+    assert emu_f64.emu_matmul(0, 4, 3, p(mod16), p(out), p(A), p(B), 2, 9, 4, 4, 0, 4, 0, 0, 1) == 0
+    assert np.array_equal(out, want)
+
+
 def test_emu_f64_ntt_extreme_values(emu_f64):
     """all coefficients q-1 / 0 / alternating: the largest un-renormalised legs the FP64 butterflies see"""
     for n, depth, bits in [(4096, 2, 51), (16384, 1, 51), (32768, 1, 51), (8192, 1, 33)]:
