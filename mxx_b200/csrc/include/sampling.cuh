@@ -212,25 +212,35 @@ struct KarneyMachine {
         if ((bn & 1) == 0) b_check();
         else restart();
     }
+    // The six H states share one body and so do the two B states: lanes of a warp that sit in different states of the
+    // same test then execute the same instructions (ncu: with one case body per state, half of the warp instructions
+    // of the sampler kernels ran with fewer than 4 active lanes, profiles/r01_ncu_sampler.txt).
     GP_HD void step(uint64_t w) {
         const double u = ChaChaStream::to_unit(w);
+        if (st <= kPH2) {
+            // H: a = U, !(a < 1/2) -> true; b = U, !(b < a) -> false; a = U, !(a < b) -> true; ...
+            const bool in_g = st < kPH0;
+            const uint32_t sub = in_g ? st : st - kPH0;
+            const double thr = sub == 0 ? 0.5 : hv;
+            if (u < thr) hv = u, st = st - sub + (sub == 1 ? 2u : 1u);
+            else h_result(sub != 1, in_g);
+            return;
+        }
+        if (st == kB0 || st == kB1) {
+            // B: z = U, !(z < y) ends; r = U, !(r < (2k + x) / (2k + 2)) ends; y = z; ...
+            const bool first = st == kB0;
+            const double thr = first ? y : (2.0 * (double)k + x) / (double)(2 * k + 2);
+            if (first) z = u;
+            if (!(u < thr)) b_result();
+            else if (first) st = kB1;
+            else {
+                y = z;
+                if (bn > 4096) b_result();
+                else ++bn, st = kB0;
+            }
+            return;
+        }
         switch (st) {
-            case kGH0:
-            case kPH0:  // H: a = U; !(a < 1/2) -> true
-                hv = u;
-                if (!(u < 0.5)) h_result(true, st == kGH0);
-                else st += 1;
-                break;
-            case kGH1:
-            case kPH1:  // b = U; !(b < a) -> false
-                if (!(u < hv)) h_result(false, st == kGH1);
-                else hv = u, st += 1;
-                break;
-            case kGH2:
-            case kPH2:  // a = U; !(a < b) -> true
-                if (!(u < hv)) h_result(true, st == kGH2);
-                else hv = u, st -= 1;
-                break;
             case kSign: {
                 sgn = (w & 1ULL) ? 1 : -1;
                 const double di0 = sd * (double)k + (double)sgn * mean;
@@ -244,19 +254,6 @@ struct KarneyMachine {
                 x = x0 + (double)j / sd;
                 if (!(x < 1.0) || (x == 0.0 && sgn < 0 && k == 0)) restart();
                 else h = k + 1, b_check();
-                break;
-            case kB0:  // z = U; !(z < y) ends B
-                z = u;
-                if (!(u < y)) b_result();
-                else st = kB1;
-                break;
-            case kB1:  // r = U; !(r < (2k + x) / (2k + 2)) ends B
-                if (!(u < (2.0 * (double)k + x) / (double)(2 * k + 2))) b_result();
-                else {
-                    y = z;
-                    if (bn > 4096) b_result();
-                    else ++bn, st = kB0;
-                }
                 break;
             case kFb1:
                 hv = u, st = kFb2;
