@@ -96,6 +96,8 @@ CASES = [
     (16384, 1, 61, 0, 0),
     (32768, 1, 51, 0, 0),   # 2^13 blocks under a radix-4 global pass
     (65536, 1, 61, 0, 0),
+    (16384, 1, 55, 0, 0),   # u64 integer NOCSUB plan above the FP64 range
+    (32768, 1, 55, 0, 0),
     (16384, 1, 24, 0, 1),   # u64 storage forced for a small modulus
     (16384, 1, 24, 14, 0),  # same ring through the generic kernel
 ]

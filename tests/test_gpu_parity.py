@@ -52,6 +52,8 @@ PARAMS = [
     (32768, 1, 51, 17),
     (65536, 1, 28, 14),
     (65536, 1, 51, 26),
+    (16384, 2, 55, 19),   # u64 integer kernels without conditional subtractions (moduli in [2^51, 2^58): not on the FP64 pipe)
+    (32768, 1, 55, 19),
 ]
 
 
@@ -178,6 +180,44 @@ def test_mul_decompose_matches_oracle(mx, n, depth, bits, bb, r, d, c, small):
     assert np.array_equal(seq.to_rns(), want)
     assert gS * (gO.small_decompose() if small else gO.decompose()) == fused
     assert np.array_equal(gO.to_rns(), other)  # inputs untouched
+
+
+KNOB_SCRIPT = """
+import sys
+import numpy as np
+sys.path.insert(0, {root!r})
+import mxx_b200 as mx
+from oracle import oracle as orc
+for n, depth, bits, bb in [(16384, 2, 51, 17), (32768, 1, 51, 17)]:
+    moduli = mx.standard_moduli(n, depth, bits)
+    params, plan = mx.GpuDCRTPolyParams(n, moduli, bb), orc.Plan(n, moduli)
+    a = plan.uniform(1, 2, seed=3)
+    g = mx.GpuDCRTPolyMatrix.from_rns(params, a, False)
+    g.ntt_in_place()
+    assert np.array_equal(g.to_rns(), plan.ntt(a))
+    g.intt_all_in_place()
+    assert np.array_equal(g.to_rns(), a)
+    ell = plan.ell(bb, False)
+    S, other = plan.uniform(2, ell, seed=10), plan.uniform(1, 2, seed=11)
+    got = mx.GpuDCRTPolyMatrix.from_rns(params, S, True).mul_decompose(mx.GpuDCRTPolyMatrix.from_rns(params, other, True), fused=True)
+    assert np.array_equal(got.to_rns(), plan.mul_decompose(S, other, bb, False))
+print("knobs ok")
+"""
+
+
+@pytest.mark.parametrize("knobs", [{"MXX_NTT_F64": "0"}, {"MXX_MATMUL_F64": "0"}, {"MXX_DECOMP_FUSE_TOP": "0"},
+                                   {"MXX_NTT_F64": "0", "MXX_MATMUL_F64": "0", "MXX_DECOMP_FUSE_TOP": "0"}])
+def test_kernel_selection_knobs_keep_results(mx, knobs):
+    """51-bit contexts default to the FP64-pipe NTT / product and the fused top pass; with each knob off the integer
+    kernels must give the same (oracle) results.  The knobs are read at context creation, hence a fresh process."""
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, **knobs)
+    out = subprocess.run([sys.executable, "-c", KNOB_SCRIPT.format(root=root)], env=env, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "knobs ok" in out.stdout, out.stderr[-2000:]
 
 
 def test_mul_decompose_chunked_workspace(mx, monkeypatch):
