@@ -63,8 +63,8 @@ template <typename T> int run_matmul(GpuContext *ctx, T *out, const T *A, const 
     if constexpr (sizeof(T) == 8) {
         if (ctx->f64_ntt && ctx->f64_matmul) {  // moduli < 2^51: the product on the FP64 pipe (arith.cuh)
             g.fold = ctx->f64_mac_fold;
-            if (g.rows >= 4) return launch_matmul_f64_tile<VMAX / 2, 4, 4>(ctx, out, A, B, g);
-            if (g.rows >= 2) return launch_matmul_f64_tile<VMAX, 2, 4>(ctx, out, A, B, g);
+            if (g.rows >= 4) return launch_matmul_f64_tile<VMAX / 2, 4, 4, 1>(ctx, out, A, B, g);
+            if (g.rows >= 2) return launch_matmul_f64_tile<VMAX, 2, 4, 1>(ctx, out, A, B, g);
             if (g.cols % 6 == 0) return launch_matmul_f64_tile<VMAX, 1, 6, 2, 64>(ctx, out, A, B, g);
             return launch_matmul_f64_tile<VMAX, 1, 1, 6, 128>(ctx, out, A, B, g);
         }
