@@ -101,7 +101,13 @@ template <typename T, int LOGB> struct FastCfg {
 #define GP_FAST_MINB 3
 #endif
     static constexpr int kThreads = kSmall ? GP_FAST_THREADS : 512;
-    static constexpr int kMinBlocks = kSmall ? (sizeof(T) == 4 ? GP_FAST_MINB : 2) : 1;
+#ifndef GP_FAST_MINB_WIDE
+#define GP_FAST_MINB_WIDE 2
+#endif
+#ifndef GP_FAST_MINB_F64
+#define GP_FAST_MINB_F64 3  // the FP64 butterflies fit 80 registers: a third resident CTA gives +10 % (tools/ntt_lab.cu)
+#endif
+    static constexpr int kMinBlocks = kSmall ? (sizeof(T) == 4 ? GP_FAST_MINB : (is_f64<T>::value ? GP_FAST_MINB_F64 : GP_FAST_MINB_WIDE)) : 1;
 };
 
 // ---- asynchronous global -> shared staging (LDGSTS) ---------------------------------------------
