@@ -9,7 +9,7 @@ mkdir -p gpurun_out
 for what in "$@"; do
   python tools/prof_kernels.py $what > gpurun_out/plain_${what}.log 2>&1 || { echo "plain run of $what failed"; continue; }
   rep=/tmp/${tag}_${what}
-  ncu --set full --clock-control none --import-source on -k regex:"fast_|matmul_kernel|global_pass|decompose|mac" -s ${SKIP:-0} -c ${COUNT:-6} \
+  ncu --set full --clock-control none --import-source on -k regex:"fast_|matmul_kernel|matmul_f64|global_pass|decompose|mac" -s ${SKIP:-0} -c ${COUNT:-6} \
       -o $rep -f python tools/prof_kernels.py $what > gpurun_out/ncu_${what}.log 2>&1
   ncu -i $rep.ncu-rep --page raw --csv > gpurun_out/${tag}_${what}_raw.csv 2>/dev/null
   ncu -i $rep.ncu-rep --page source --csv > gpurun_out/${tag}_${what}_source.csv 2>/dev/null
