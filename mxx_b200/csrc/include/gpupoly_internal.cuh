@@ -77,6 +77,7 @@ struct GpuContext {
     bool fuse_decompose_top = true;  // MXX_DECOMP_FUSE_TOP=0: separate digit kernel + first global pass (A/B)
     bool force_generic_ntt = false;  // MXX_NTT_GENERIC=1: use only the runtime-planned kernels of ntt.cuh
     int ntt_block_override = 0;      // MXX_NTT_BLOCK_LOG
+    bool ntt_cluster = true;         // MXX_NTT_CLUSTER=0: rings above one block go back to global passes + block kernel (A/B)
     bool smem_configured = false;  // >48 KB dynamic shared memory opted in for the NTT kernels
     bool f64_matmul = true;      // MXX_MATMUL_F64=0: keep the 128-bit integer MAC in FP64-pipe contexts (A/B)
     uint32_t f64_mac_fold = 1;   // reduced terms between renormalisations of the FP64 accumulator

@@ -582,14 +582,11 @@ GP_HD void i_last(const SmemView<T, LOGB> &sm, T *__restrict__ dst, const TwPair
 }
 
 // ---- whole-block transforms ------------------------------------------------------------------------
-template <typename T, int LOGB, bool NOCSUB, class Src>
-GP_HD void fast_fwd_block(const Src &src, T *__restrict__ dst, void *smem, uint32_t logn, uint32_t sb,
-                          const TwPair<T> *__restrict__ tw, const LimbConst<T> &c) {
+// everything after pass 1 of a forward block: the radix-16 shared-memory passes and the radix-4 store pass
+template <typename T, int LOGB, bool NOCSUB>
+GP_HD void fast_fwd_tail(const SmemView<T, LOGB> &sm, T *__restrict__ dst, uint32_t nblk, uint32_t sb,
+                         const TwPair<T> *__restrict__ tw, const LimbConst<T> &c) {
     using G = FastGeom<LOGB>;
-    const SmemView<T, LOGB> sm(smem);
-    const uint32_t nblk = 1u << (logn - LOGB);
-    f_first<T, LOGB, NOCSUB>(src, sm, tw, nblk, sb, c.q, c.q2);
-    GP_SYNC();
     constexpr int S1 = LOGB - G::kR1;  // span after pass 1
     if constexpr (G::kK >= 1) {
         f_mid<T, LOGB, S1, NOCSUB>(sm, tw, nblk, sb, c.q, c.q2);
@@ -606,13 +603,21 @@ GP_HD void fast_fwd_block(const Src &src, T *__restrict__ dst, void *smem, uint3
     static_assert(G::kK <= 3, "add another f_mid");
     f_last<T, LOGB, NOCSUB, LOGB>(sm, dst, tw, nblk, sb, c);
 }
-
-template <typename T, int LOGB, bool FINAL>
-GP_HD void fast_inv_block(const T *__restrict__ src, T *__restrict__ dst, void *smem, uint32_t logn, uint32_t sb,
+template <typename T, int LOGB, bool NOCSUB, class Src>
+GP_HD void fast_fwd_block(const Src &src, T *__restrict__ dst, void *smem, uint32_t logn, uint32_t sb,
                           const TwPair<T> *__restrict__ tw, const LimbConst<T> &c) {
-    using G = FastGeom<LOGB>;
     const SmemView<T, LOGB> sm(smem);
     const uint32_t nblk = 1u << (logn - LOGB);
+    f_first<T, LOGB, NOCSUB>(src, sm, tw, nblk, sb, c.q, c.q2);
+    GP_SYNC();
+    fast_fwd_tail<T, LOGB, NOCSUB>(sm, dst, nblk, sb, tw, c);
+}
+
+// everything before the last pass of an inverse block: the radix-4 load pass and the radix-16 shared-memory passes
+template <typename T, int LOGB>
+GP_HD void fast_inv_head(const T *__restrict__ src, const SmemView<T, LOGB> &sm, uint32_t nblk, uint32_t sb,
+                         const TwPair<T> *__restrict__ tw, const LimbConst<T> &c) {
+    using G = FastGeom<LOGB>;
     i_first<T, LOGB>(src, sm, tw, nblk, sb, c);
     GP_SYNC();
     if constexpr (G::kK >= 1) {
@@ -627,6 +632,13 @@ GP_HD void fast_inv_block(const T *__restrict__ src, T *__restrict__ dst, void *
         i_mid<T, LOGB, 10>(sm, tw, nblk, sb, c);
         GP_SYNC();
     }
+}
+template <typename T, int LOGB, bool FINAL>
+GP_HD void fast_inv_block(const T *__restrict__ src, T *__restrict__ dst, void *smem, uint32_t logn, uint32_t sb,
+                          const TwPair<T> *__restrict__ tw, const LimbConst<T> &c) {
+    const SmemView<T, LOGB> sm(smem);
+    const uint32_t nblk = 1u << (logn - LOGB);
+    fast_inv_head<T, LOGB>(src, sm, nblk, sb, tw, c);
     i_last<T, LOGB, FINAL>(sm, dst, tw, nblk, sb, c);
 }
 

@@ -166,6 +166,7 @@ int gpu_context_create(uint32_t logN, uint32_t L, uint32_t dnum, const uint64_t 
         if (const char *env = getenv("MXX_NTT_GENERIC")) ctx->force_generic_ntt = env[0] == '1';
         if (const char *env = getenv("MXX_DECOMP_FUSE_TOP")) ctx->fuse_decompose_top = env[0] != '0';
         if (const char *env = getenv("MXX_NTT_BLOCK_LOG")) ctx->ntt_block_override = atoi(env);
+        if (const char *env = getenv("MXX_NTT_CLUSTER")) ctx->ntt_cluster = env[0] != '0';
         GP_CUDA(cudaSetDevice(ctx->device), "cudaSetDevice");
         cudaDeviceProp prop;
         GP_CUDA(cudaGetDeviceProperties(&prop, ctx->device), "cudaGetDeviceProperties");

@@ -11,6 +11,7 @@
 //
 // Data crosses this interface as u64 words in DEVICE order ([poly][limb][coeff], EVAL
 // bit-reversed); `wide` picks the storage width exactly like gpu_context_create does.
+#define GP_EMU_BUILD 1
 #include <stdint.h>
 #include <string.h>
 
@@ -20,6 +21,7 @@
 #include "host_tables.hpp"
 #include "ntt.cuh"
 #include "ntt_fast.cuh"
+#include "ntt_cluster.cuh"
 #include "sampling.cuh"
 
 namespace {
@@ -27,6 +29,7 @@ using namespace gp;
 
 size_t g_f64_blocks = 0;  // blocks run through F64 kernels (tests assert the path was really taken)
 int g_fuse_top = 1;  // emu_set_fuse_top: digits extracted inside the first global pass (the launcher's default)
+int g_cluster = 1;  // emu_set_cluster: rings of 2..8 blocks through the cluster / DSMEM phases (the launcher's default)
 int g_f64 = 0;  // emu_set_f64: drive the FP64-pipe kernels (type F64) where the product library would
 
 template <typename T> struct Emu {
@@ -97,6 +100,107 @@ template <typename T> struct Emu {
                 if constexpr (sizeof(T) == 4) fast_inv_blocks<15>(d, nbid);
         }
     }
+    // ---- cluster / DSMEM kernels (ntt_cluster.cuh), phase by phase: every rank's push (pull) runs before any rank's
+    // local (store) phase, which is what the cluster barrier guarantees on the device ----
+    int cluster_lc(int logb_cap) const { return (g_cluster && logb_cap == 0) ? cluster_log<T>(logn) : 0; }
+    template <typename K, int LB, int LC, bool NOCSUB, class MakeSrc>
+    void cluster_fwd_run(K *dst, size_t pl_count, const TwPair<K> *tw_all, const LimbConst<K> *lc, MakeSrc make_src) {
+        constexpr int C = 1 << LC;
+        std::vector<std::vector<uint32_t>> bufs(C, std::vector<uint32_t>(fast_smem_bytes<K, LB>() / 4 + 4));
+        ClusterPeersHost<K, LB, LC> peers;
+        for (int j = 0; j < C; j++) peers.base[j] = bufs[j].data();
+        for (size_t pl = 0; pl < pl_count; pl++) {
+            const uint32_t limb = (uint32_t)(pl % limbs);
+            const LimbConst<K> c = lc[limb];
+            const TwPair<K> *tw = tw_all + ((size_t)limb << logn);
+            const auto src = make_src(pl, c);
+            for (uint32_t r = 0; r < (uint32_t)C; r++) cl_fwd_push<K, LB, LC, NOCSUB>(src, peers, r, tw, c.q, c.q2);
+            for (uint32_t r = 0; r < (uint32_t)C; r++)
+                cl_fwd_local<K, LB, LC, NOCSUB>(bufs[r].data(), dst + (pl << logn) + ((size_t)r << LB), r, tw, c);
+        }
+    }
+    template <typename K, int LB, int LC>
+    void cluster_inv_run(const K *src, K *dst, size_t pl_count, const TwPair<K> *tw_all, const LimbConst<K> *lc) {
+        constexpr int C = 1 << LC;
+        std::vector<std::vector<uint32_t>> bufs(C, std::vector<uint32_t>(fast_smem_bytes<K, LB>() / 4 + 4));
+        ClusterPeersHost<K, LB, LC> peers;
+        for (int j = 0; j < C; j++) peers.base[j] = bufs[j].data();
+        for (size_t pl = 0; pl < pl_count; pl++) {
+            const uint32_t limb = (uint32_t)(pl % limbs);
+            const LimbConst<K> c = lc[limb];
+            const TwPair<K> *tw = tw_all + ((size_t)limb << logn);
+            for (uint32_t r = 0; r < (uint32_t)C; r++)
+                cl_inv_local<K, LB, LC>(src + (pl << logn) + ((size_t)r << LB), bufs[r].data(), r, tw, c);
+            for (uint32_t r = 0; r < (uint32_t)C; r++) cl_inv_pull<K, LB, LC>(peers, dst + (pl << logn), r, tw, c);
+        }
+    }
+    // MakeSrc for the working type K (plain words of `d`, or digits of `s` under geometry g)
+    template <typename K, int LC, class MakeSrc> void cluster_fwd_any(K *dst, size_t pl_count, MakeSrc make_src) {
+        constexpr int LB = sizeof(T) == 4 ? 14 : 13;
+        if constexpr (is_f64<K>::value) {
+            g_f64_blocks += pl_count << LC;
+            cluster_fwd_run<K, LB, LC, false>(dst, pl_count, ftab.fwd.data(), ftab.limb.data(), make_src);
+        } else {
+            if (nocsub) cluster_fwd_run<K, LB, LC, true>(dst, pl_count, tab.fwd.data(), tab.limb.data(), make_src);
+            else cluster_fwd_run<K, LB, LC, false>(dst, pl_count, tab.fwd.data(), tab.limb.data(), make_src);
+        }
+    }
+    template <typename K, class MakeSrc> void cluster_fwd_lc(int lc, K *dst, size_t pl_count, MakeSrc make_src) {
+        switch (lc) {
+            case 1: cluster_fwd_any<K, 1>(dst, pl_count, make_src); break;
+            case 2: cluster_fwd_any<K, 2>(dst, pl_count, make_src); break;
+            default: cluster_fwd_any<K, 3>(dst, pl_count, make_src); break;
+        }
+    }
+    void cluster_fwd(std::vector<T> &d, size_t polys, int lc) {
+        const size_t pl = polys * limbs;
+        const int ln = logn;
+        if constexpr (sizeof(T) == 8) {
+            if (f64) {
+                const F64 *base = (const F64 *)d.data();
+                cluster_fwd_lc<F64>(lc, (F64 *)d.data(), pl, [base, ln](size_t p, const LimbConst<F64> &c) { return PlainSrc<F64>{base + (p << ln), 4 * (uint64_t)c.q.v}; });
+                return;
+            }
+        }
+        const T *base = d.data();
+        cluster_fwd_lc<T>(lc, d.data(), pl, [base, ln](size_t p, const LimbConst<T> &) { return PlainSrc<T>{base + (p << ln)}; });
+    }
+    void cluster_decompose(const std::vector<T> &s, std::vector<T> &o, const DecompGeom &g, size_t opl, int lc) {
+        const int ln = logn;
+        if constexpr (sizeof(T) == 8) {
+            if (f64) {
+                const F64 *sp = (const F64 *)s.data();
+                const LimbConst<F64> *lcf = ftab.limb.data();
+                cluster_fwd_lc<F64>(lc, (F64 *)o.data(), opl, [sp, g, ln, lcf](size_t p, const LimbConst<F64> &) { return make_digit_src<F64>(sp, g, p, (uint32_t)ln, lcf); });
+                return;
+            }
+        }
+        const T *sp = s.data();
+        const LimbConst<T> *lct = tab.limb.data();
+        cluster_fwd_lc<T>(lc, o.data(), opl, [sp, g, ln, lct](size_t p, const LimbConst<T> &) { return make_digit_src<T>(sp, g, p, (uint32_t)ln, lct); });
+    }
+    void cluster_inv(std::vector<T> &d, size_t polys, int lc) {
+        const size_t pl = polys * limbs;
+        constexpr int LB = sizeof(T) == 4 ? 14 : 13;
+#define EMU_CINV(K, LC, TW, LCT) cluster_inv_run<K, LB, LC>((const K *)d.data(), (K *)d.data(), pl, TW, LCT)
+        if constexpr (sizeof(T) == 8) {
+            if (f64) {
+                g_f64_blocks += pl << lc;
+                switch (lc) {
+                    case 1: EMU_CINV(F64, 1, ftab.inv.data(), ftab.limb.data()); break;
+                    case 2: EMU_CINV(F64, 2, ftab.inv.data(), ftab.limb.data()); break;
+                    default: EMU_CINV(F64, 3, ftab.inv.data(), ftab.limb.data()); break;
+                }
+                return;
+            }
+        }
+        switch (lc) {
+            case 1: EMU_CINV(T, 1, tab.inv.data(), tab.limb.data()); break;
+            case 2: EMU_CINV(T, 2, tab.inv.data(), tab.limb.data()); break;
+            default: EMU_CINV(T, 3, tab.inv.data(), tab.limb.data()); break;
+        }
+#undef EMU_CINV
+    }
     bool nocsub = false;
     int block_log(int logb_cap) const {
         if (fast_ok(logb_cap)) return fast_block_log<T>(logn);
@@ -105,6 +209,7 @@ template <typename T> struct Emu {
         return lb;
     }
     void fwd(std::vector<T> &d, size_t polys, int logb_cap, bool first_top_pass_done = false) {
+        if (const int lc = cluster_lc(logb_cap); lc > 0 && !first_top_pass_done) return cluster_fwd(d, polys, lc);
         const int logb = block_log(logb_cap), top = logn - logb;
         const size_t pl = polys * limbs;
         std::vector<T> sm(ntt_smem_bytes<T>(logb) / sizeof(T) + 1);
@@ -131,6 +236,7 @@ template <typename T> struct Emu {
             ntt_fwd_cta<T>((uint32_t)bid, sm.data(), d.data(), d.data(), limbs, logn, logb, tab.fwd.data(), tab.limb.data());
     }
     void inv(std::vector<T> &d, size_t polys, int logb_cap) {
+        if (const int lc = cluster_lc(logb_cap); lc > 0) return cluster_inv(d, polys, lc);
         const int logb = block_log(logb_cap), top = logn - logb;
         const size_t pl = polys * limbs;
         std::vector<T> sm(ntt_smem_bytes<T>(logb) / sizeof(T) + 1);
@@ -208,7 +314,9 @@ int do_decompose(int logn, uint32_t limbs, const uint64_t *moduli, const uint64_
     std::vector<T> o(opl << logn);
     const int logb = e.block_log(logb_cap), top = logn - logb;
     std::vector<T> sm(ntt_smem_bytes<T>(logb) / sizeof(T) + 1);
-    if (to_eval && top == 0 && e.fast_ok(logb_cap)) {
+    if (const int lc = e.cluster_lc(logb_cap); to_eval && lc > 0) {
+        e.cluster_decompose(s, o, g, opl, lc);
+    } else if (to_eval && top == 0 && e.fast_ok(logb_cap)) {
         std::vector<uint32_t> fsm((sizeof(T) / 4) * ((1u << logb) + (1u << (logb - 4))) + 8);
 #define DEC_CASE(LB)                                                                                                          \
     case LB:                                                                                                                  \
@@ -450,6 +558,7 @@ int emu_sample_p1(int force_wide, int logn, uint32_t limbs, const uint64_t *modu
     } catch (...) { return 1; }
 }
 void emu_set_f64(int on) { g_f64 = on; }
+void emu_set_cluster(int on) { g_cluster = on; }
 void emu_set_fuse_top(int on) { g_fuse_top = on; }
 size_t emu_f64_blocks(void) { return g_f64_blocks; }
 // force_wide: 0 = the context rule (u32 words when all moduli < 2^30), 1 = u64 words regardless

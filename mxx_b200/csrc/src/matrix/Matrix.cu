@@ -14,6 +14,7 @@
 #include "arith.cuh"
 #include "ntt.cuh"
 #include "ntt_fast.cuh"
+#include "ntt_cluster.cuh"
 #include "serde.cuh"
 #include "compact.cuh"
 #include "sampling.cuh"

@@ -23,26 +23,47 @@ int launch_elementwise(GpuContext *ctx, T *out, const T *a, const T *b, size_t w
     return 0;
 }
 
+// grid.y / grid.z hold the column / row tiles and are limited to 65535: wider products go out in slabs
+// (the reference accepts any size, cuda/src/matrix/MatrixArith.cu:2886-2904)
+constexpr uint32_t kMaxGridYZ = 65535;
+template <class Launch> int for_each_matmul_slab(const gp::MatmulGeom &g, int TR, int TC, size_t poly_words, Launch launch) {
+    const uint32_t col_slab = kMaxGridYZ * (uint32_t)TC, row_slab = kMaxGridYZ * (uint32_t)TR;
+    for (uint32_t r0 = 0; r0 < g.rows; r0 += row_slab)
+        for (uint32_t c0 = 0; c0 < g.cols; c0 += col_slab) {
+            gp::MatmulGeom s = g;
+            s.rows = std::min(row_slab, g.rows - r0);
+            s.cols = std::min(col_slab, g.cols - c0);
+            s.b_col0 = g.b_col0 + c0;
+            s.out_col0 = g.out_col0 + c0;
+            if (launch(s, (size_t)r0 * g.inner * poly_words, (size_t)r0 * g.out_cols * poly_words)) return 1;
+        }
+    return 0;
+}
+
 template <typename T, int V, int TR, int TC, int UNROLL = 2, int NT = 128>
 int launch_matmul_tile(GpuContext *ctx, T *out, const T *A, const T *B, const gp::MatmulGeom &g) {
     const unsigned threads = NT;
     const unsigned per_limb = (unsigned)(((size_t)ctx->N / V + threads - 1) / threads);
-    dim3 grid(g.limbs * per_limb, (g.cols + TC - 1) / TC, (g.rows + TR - 1) / TR);
-    gp::matmul_kernel<T, V, TR, TC, UNROLL, NT><<<grid, threads, 0, gp::cur(ctx)>>>(out, A, B, g, (const gp::LimbConst<T> *)ctx->d_limb);
-    gp::count_launch();
-    GP_CHECK_LAUNCH("matmul_kernel");
-    return 0;
+    return for_each_matmul_slab(g, TR, TC, (size_t)g.limbs << g.logn, [&](const gp::MatmulGeom &s, size_t a_off, size_t o_off) {
+        dim3 grid(s.limbs * per_limb, (s.cols + TC - 1) / TC, (s.rows + TR - 1) / TR);
+        gp::matmul_kernel<T, V, TR, TC, UNROLL, NT><<<grid, threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, (const gp::LimbConst<T> *)ctx->d_limb);
+        gp::count_launch();
+        GP_CHECK_LAUNCH("matmul_kernel");
+        return 0;
+    });
 }
 
 template <int V, int TR, int TC, int UNROLL = 2, int NT = 128>
 int launch_matmul_f64_tile(GpuContext *ctx, uint64_t *out, const uint64_t *A, const uint64_t *B, const gp::MatmulGeom &g) {
     const unsigned threads = NT;
     const unsigned per_limb = (unsigned)(((size_t)ctx->N / V + threads - 1) / threads);
-    dim3 grid(g.limbs * per_limb, (g.cols + TC - 1) / TC, (g.rows + TR - 1) / TR);
-    gp::matmul_f64_kernel<V, TR, TC, UNROLL, NT><<<grid, threads, 0, gp::cur(ctx)>>>(out, A, B, g, (const gp::LimbConst<gp::F64> *)ctx->d_limb_f64);
-    gp::count_launch();
-    GP_CHECK_LAUNCH("matmul_f64_kernel");
-    return 0;
+    return for_each_matmul_slab(g, TR, TC, (size_t)g.limbs << g.logn, [&](const gp::MatmulGeom &s, size_t a_off, size_t o_off) {
+        dim3 grid(s.limbs * per_limb, (s.cols + TC - 1) / TC, (s.rows + TR - 1) / TR);
+        gp::matmul_f64_kernel<V, TR, TC, UNROLL, NT><<<grid, threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, (const gp::LimbConst<gp::F64> *)ctx->d_limb_f64);
+        gp::count_launch();
+        GP_CHECK_LAUNCH("matmul_f64_kernel");
+        return 0;
+    });
 }
 
 // out[:, out_col0 : out_col0+cols] = A(rows x inner) * B[:, b_col0 : b_col0+cols]

@@ -16,9 +16,18 @@ uint64_t host_powmod(uint64_t b, uint64_t e, uint64_t q) {
     return (uint64_t)r;
 }
 
+// gpu_matrix_fill_gadget takes the widest modulus among the matrix's ACTIVE limbs (cuda/src/matrix/MatrixDecompose.cu:346-355);
+// decompose and gauss_samp use all moduli of the context (:924-935) — digits_per_tower(ctx, ...)
+uint32_t gadget_digits_per_tower(const GpuMatrix *m, uint32_t base_bits) {
+    uint32_t bits = 0;
+    for (size_t i = 0; i < m->limbs() && i < m->ctx->moduli.size(); i++)
+        bits = std::max(bits, 64u - (uint32_t)__builtin_clzll(m->ctx->moduli[i]));
+    return (bits + base_bits - 1) / base_bits;
+}
+
 template <typename T>
 int run_fill_gadget(GpuContext *ctx, GpuMatrix *out, uint32_t base_bits, bool small) {
-    const uint32_t dpt = digits_per_tower(ctx, base_bits), limbs = (uint32_t)out->limbs();
+    const uint32_t dpt = gadget_digits_per_tower(out, base_bits), limbs = (uint32_t)out->limbs();
     const uint32_t ell = small ? dpt : dpt * limbs;
     std::vector<T> pow((size_t)limbs * dpt);
     for (uint32_t l = 0; l < limbs; l++)
@@ -42,7 +51,7 @@ int fill_gadget_common(GpuMatrix *out, uint32_t base_bits, bool small, const cha
     if (base_bits == 0 || base_bits >= 63) return gp::set_error(std::string("invalid base_bits in ") + name);  // :316
     if (out->level < 0) return gp::set_error(std::string("invalid level in ") + name);
     GpuContext *ctx = out->ctx;
-    const size_t dpt = digits_per_tower(ctx, base_bits);
+    const size_t dpt = gadget_digits_per_tower(out, base_bits);
     const size_t ell = small ? dpt : dpt * out->limbs();
     if (out->cols != out->rows * ell) return gp::set_error(std::string("output size mismatch in ") + name);  // :363
     out->format = GPU_POLY_FORMAT_EVAL;  // :431-437
@@ -74,6 +83,30 @@ template <typename T> int dispatch_fast_decompose(GpuContext *ctx, const T *src,
     }
 }
 
+template <typename K, int LOGB, int LC, bool NOCSUB>
+int launch_cluster_decompose(GpuContext *ctx, const K *src, K *out, const gp::DecompGeom &g, size_t opl) {
+    static std::atomic<uint32_t> done{0};
+    constexpr size_t smem = gp::fast_smem_bytes<K, LOGB>();
+    auto kernel = gp::fast_decompose_cluster_kernel<K, LOGB, LC, NOCSUB>;
+    if (optin_smem(kernel, smem, ctx->device, done)) return 1;
+    kernel<<<(unsigned)(opl << LC), gp::FastCfg<K, LOGB>::kThreads, smem, gp::cur(ctx)>>>(src, out, g, fwd_tab<K>(ctx), limb_tab<K>(ctx));
+    gp::count_launch();
+    GP_CHECK_LAUNCH("fast_decompose_cluster_kernel");
+    return 0;
+}
+template <typename K> int dispatch_cluster_decompose(GpuContext *ctx, const K *src, K *out, const gp::DecompGeom &g, size_t opl, int lc) {
+    constexpr int LB = sizeof(K) == 4 ? 14 : 13;
+    if constexpr (gp::is_f64<K>::value) {
+#define GP_CALL(LC) launch_cluster_decompose<K, LB, LC, false>(ctx, src, out, g, opl)
+        GP_CLUSTER_SWITCH(lc, GP_CALL)
+#undef GP_CALL
+    } else {
+#define GP_CALL(LC) (ctx->nocsub ? launch_cluster_decompose<K, LB, LC, true>(ctx, src, out, g, opl) : launch_cluster_decompose<K, LB, LC, false>(ctx, src, out, g, opl))
+        GP_CLUSTER_SWITCH(lc, GP_CALL)
+#undef GP_CALL
+    }
+}
+
 // out (rows*ell x cols) <- digits of src[:, src_col0 : src_col0 + cols] (src in COEFF form)
 template <typename T>
 int run_decompose(GpuContext *ctx, const T *src_coeff, T *out, size_t rows, size_t src_cols, size_t src_col0, size_t cols,
@@ -89,6 +122,12 @@ int run_decompose(GpuContext *ctx, const T *src_coeff, T *out, size_t rows, size
     g.base_bits = base_bits;
     const size_t opl = rows * g.ell * cols * limbs;
     if (opl == 0) return 0;
+    if (const int lc = ntt_cluster_log<T>(ctx); to_eval && lc > 0) {  // rings of 2..8 blocks: digits extracted by the cluster's push phase
+        if constexpr (sizeof(T) == 8) {
+            if (ctx->f64_ntt) return dispatch_cluster_decompose<gp::F64>(ctx, (const gp::F64 *)src_coeff, (gp::F64 *)out, g, opl, lc);
+        }
+        return dispatch_cluster_decompose<T>(ctx, src_coeff, out, g, opl, lc);
+    }
     const int logn = ctx->logN, logb = ntt_block_log<T>(ctx), top = logn - logb;
     if (to_eval && top == 0 && use_fast<T>(ctx, logb)) {
         if constexpr (sizeof(T) == 8) {

@@ -158,10 +158,12 @@ LoadPipe *get_load_pipe(GpuContext *ctx) {
 }
 
 template <typename S>
-int launch_pack_from(GpuContext *ctx, cudaStream_t stream, uint32_t *dst, const S *src, size_t words, bool bitrev) {
+int launch_pack_from(GpuContext *ctx, cudaStream_t stream, uint32_t *dst, const S *src, size_t words, bool bitrev, size_t word0,
+                     uint32_t limbs) {
     const unsigned threads = 256, grid = stride_grid(ctx, words, threads);
-    if (bitrev) gp::pack_kernel<uint32_t, S, true><<<grid, threads, 0, stream>>>(dst, src, words, (uint32_t)ctx->logN);
-    else gp::pack_kernel<uint32_t, S, false><<<grid, threads, 0, stream>>>(dst, src, words, (uint32_t)ctx->logN);
+    const auto *lc = (const gp::LimbConst<uint32_t> *)ctx->d_limb;
+    if (bitrev) gp::pack_kernel<uint32_t, S, true><<<grid, threads, 0, stream>>>(dst, src, words, (uint32_t)ctx->logN, word0, limbs, lc);
+    else gp::pack_kernel<uint32_t, S, false><<<grid, threads, 0, stream>>>(dst, src, words, (uint32_t)ctx->logN, word0, limbs, lc);
     gp::count_launch();
     GP_CHECK_LAUNCH("pack_kernel(chunk)");
     return 0;
@@ -253,7 +255,13 @@ int load_hybrid(GpuContext *ctx, GpuMatrix *mat, const uint64_t *host, size_t wo
     while (finished < chunks && status == 0) {
         bool progressed = false;
         // 1. ring slots whose DMA has completed go back to the workers
-        while (!slot_inflight.empty() && cudaEventQuery(slot_inflight.front().first) == cudaSuccess) {
+        while (!slot_inflight.empty()) {
+            const cudaError_t q = cudaEventQuery(slot_inflight.front().first);
+            if (q == cudaErrorNotReady) break;
+            if (q != cudaSuccess) {  // a sticky fault: nothing will ever complete, do not spin on it
+                status = gp::set_cuda_error(q, "load pipeline (ring slot)");
+                break;
+            }
             {
                 std::lock_guard<std::mutex> g(sh.m);
                 sh.free_slots.push_back(slot_inflight.front().second);
@@ -281,7 +289,7 @@ int load_hybrid(GpuContext *ctx, GpuMatrix *mat, const uint64_t *host, size_t wo
             if (err == cudaSuccess) err = cudaEventRecord(pipe->slot_ev[item.first], s);
             if (err != cudaSuccess) { status = gp::set_cuda_error(err, "narrow-lane DMA"); break; }
             slot_inflight.emplace_back(pipe->slot_ev[item.first], item.first);
-            if (launch_pack_from<uint32_t>(ctx, s, dst + item.second * chunk_words, pipe->dev_narrow[l], len, bitrev)) { status = 1; break; }
+            if (launch_pack_from<uint32_t>(ctx, s, dst + item.second * chunk_words, pipe->dev_narrow[l], len, bitrev, item.second * chunk_words, (uint32_t)mat->limbs())) { status = 1; break; }
             enq_narrow++;
             finished++;
             progressed = true;
@@ -289,7 +297,10 @@ int load_hybrid(GpuContext *ctx, GpuMatrix *mat, const uint64_t *host, size_t wo
         // 3. lane R takes a front chunk when one of its two buffers is idle
         if (pinned_src) {
             for (int l = 0; l < 2; l++) {
-                if (raw_busy[l] && cudaEventQuery(raw_ev[l]) == cudaSuccess) raw_busy[l] = false;
+                if (!raw_busy[l]) continue;
+                const cudaError_t q = cudaEventQuery(raw_ev[l]);
+                if (q == cudaSuccess) raw_busy[l] = false;
+                else if (q != cudaErrorNotReady && status == 0) status = gp::set_cuda_error(q, "load pipeline (raw lane)");
             }
             const int l = (int)(enq_raw & 1);
             if (!raw_busy[l]) {
@@ -307,7 +318,7 @@ int load_hybrid(GpuContext *ctx, GpuMatrix *mat, const uint64_t *host, size_t wo
                     const size_t len = chunk_len(c);
                     err = cudaMemcpyAsync(pipe->dev_raw[l], host + c * chunk_words, len * 8, cudaMemcpyHostToDevice, s);
                     if (err != cudaSuccess) { status = gp::set_cuda_error(err, "raw-lane DMA"); break; }
-                    if (launch_pack_from<uint64_t>(ctx, s, dst + c * chunk_words, pipe->dev_raw[l], len, bitrev)) { status = 1; break; }
+                    if (launch_pack_from<uint64_t>(ctx, s, dst + c * chunk_words, pipe->dev_raw[l], len, bitrev, c * chunk_words, (uint32_t)mat->limbs())) { status = 1; break; }
                     err = cudaEventRecord(raw_ev[l], s);
                     if (err != cudaSuccess) { status = gp::set_cuda_error(err, "raw-lane event"); break; }
                     raw_busy[l] = true;

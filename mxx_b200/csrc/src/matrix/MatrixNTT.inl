@@ -93,6 +93,61 @@ template <typename T> int dispatch_fast_inv(GpuContext *ctx, const T *src, T *ds
 #undef GP_CALL
 }
 
+// ---- cluster / DSMEM kernels (ntt_cluster.cuh): rings of 2, 4 or 8 shared-memory blocks in ONE pass over HBM ----
+// log2(cluster size) for this context's ring, 0 = not applicable (ring fits one block, knobs, ring too large)
+template <typename T> inline int ntt_cluster_log(const GpuContext *ctx) {
+    if (!ctx->ntt_cluster || ctx->force_generic_ntt || ctx->ntt_block_override) return 0;
+    return gp::cluster_log<T>(ctx->logN);
+}
+template <typename K, int LOGB, int LC, bool NOCSUB>
+int launch_cluster_fwd(GpuContext *ctx, const K *src, K *dst, size_t pl, uint32_t limbs) {
+    static std::atomic<uint32_t> done{0};
+    constexpr size_t smem = gp::fast_smem_bytes<K, LOGB>();
+    auto kernel = gp::fast_ntt_fwd_cluster_kernel<K, LOGB, LC, NOCSUB>;
+    if (optin_smem(kernel, smem, ctx->device, done)) return 1;
+    kernel<<<(unsigned)(pl << LC), gp::FastCfg<K, LOGB>::kThreads, smem, gp::cur(ctx)>>>(src, dst, limbs, fwd_tab<K>(ctx), limb_tab<K>(ctx));
+    gp::count_launch();
+    GP_CHECK_LAUNCH("fast_ntt_fwd_cluster_kernel");
+    return 0;
+}
+template <typename K, int LOGB, int LC>
+int launch_cluster_inv(GpuContext *ctx, const K *src, K *dst, size_t pl, uint32_t limbs) {
+    static std::atomic<uint32_t> done{0};
+    constexpr size_t smem = gp::fast_smem_bytes<K, LOGB>();
+    auto kernel = gp::fast_ntt_inv_cluster_kernel<K, LOGB, LC>;
+    if (optin_smem(kernel, smem, ctx->device, done)) return 1;
+    kernel<<<(unsigned)(pl << LC), gp::FastCfg<K, LOGB>::kThreads, smem, gp::cur(ctx)>>>(src, dst, limbs, inv_tab<K>(ctx), limb_tab<K>(ctx));
+    gp::count_launch();
+    GP_CHECK_LAUNCH("fast_ntt_inv_cluster_kernel");
+    return 0;
+}
+#define GP_CLUSTER_SWITCH(lc, CALL)                                                     \
+    switch (lc) {                                                                       \
+        case 1: return CALL(1);                                                         \
+        case 2: return CALL(2);                                                         \
+        case 3: return CALL(3);                                                         \
+        default: return gp::set_error("no cluster NTT plan for this ring size");        \
+    }
+// K = the kernels' working type: T, or gp::F64 over u64 words
+template <typename K> int dispatch_cluster_fwd(GpuContext *ctx, const K *src, K *dst, size_t pl, uint32_t limbs, int lc) {
+    constexpr int LB = sizeof(K) == 4 ? 14 : 13;
+    if constexpr (gp::is_f64<K>::value) {
+#define GP_CALL(LC) launch_cluster_fwd<K, LB, LC, false>(ctx, src, dst, pl, limbs)
+        GP_CLUSTER_SWITCH(lc, GP_CALL)
+#undef GP_CALL
+    } else {
+#define GP_CALL(LC) (ctx->nocsub ? launch_cluster_fwd<K, LB, LC, true>(ctx, src, dst, pl, limbs) : launch_cluster_fwd<K, LB, LC, false>(ctx, src, dst, pl, limbs))
+        GP_CLUSTER_SWITCH(lc, GP_CALL)
+#undef GP_CALL
+    }
+}
+template <typename K> int dispatch_cluster_inv(GpuContext *ctx, const K *src, K *dst, size_t pl, uint32_t limbs, int lc) {
+    constexpr int LB = sizeof(K) == 4 ? 14 : 13;
+#define GP_CALL(LC) launch_cluster_inv<K, LB, LC>(ctx, src, dst, pl, limbs)
+    GP_CLUSTER_SWITCH(lc, GP_CALL)
+#undef GP_CALL
+}
+
 template <typename T> int ensure_ntt_smem(GpuContext *ctx, size_t bytes) {
     // opt in to > 48 KB dynamic shared memory once per context and kernel family
     if (bytes <= 48 * 1024 || ctx->smem_configured) return 0;
@@ -156,6 +211,12 @@ template <typename T>
 int run_ntt_fwd(GpuContext *ctx, const T *src, T *dst, size_t polys, uint32_t limbs, bool first_top_pass_done = false) {
     const size_t pl = polys * limbs;
     if (pl == 0) return 0;
+    if (const int lc = ntt_cluster_log<T>(ctx); lc > 0 && !first_top_pass_done) {
+        if constexpr (sizeof(T) == 8) {
+            if (ctx->f64_ntt) return dispatch_cluster_fwd<gp::F64>(ctx, (const gp::F64 *)src, (gp::F64 *)dst, pl, limbs, lc);
+        }
+        return dispatch_cluster_fwd<T>(ctx, src, dst, pl, limbs, lc);
+    }
     const int logn = ctx->logN, logb = ntt_block_log<T>(ctx), top = logn - logb;
     const bool fast = use_fast<T>(ctx, logb);
     const size_t smem = gp::ntt_smem_bytes<T>(logb);
@@ -189,6 +250,12 @@ int run_ntt_fwd(GpuContext *ctx, const T *src, T *dst, size_t polys, uint32_t li
 template <typename T> int run_ntt_inv(GpuContext *ctx, const T *src, T *dst, size_t polys, uint32_t limbs) {
     const size_t pl = polys * limbs;
     if (pl == 0) return 0;
+    if (const int lc = ntt_cluster_log<T>(ctx); lc > 0) {
+        if constexpr (sizeof(T) == 8) {
+            if (ctx->f64_ntt) return dispatch_cluster_inv<gp::F64>(ctx, (const gp::F64 *)src, (gp::F64 *)dst, pl, limbs, lc);
+        }
+        return dispatch_cluster_inv<T>(ctx, src, dst, pl, limbs, lc);
+    }
     const int logn = ctx->logN, logb = ntt_block_log<T>(ctx), top = logn - logb;
     const bool fast = use_fast<T>(ctx, logb);
     const size_t smem = gp::ntt_smem_bytes<T>(logb);

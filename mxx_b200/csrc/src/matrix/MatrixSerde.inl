@@ -24,12 +24,13 @@ int make_event_set(GpuContext *ctx, GpuEventSet **out_events) {
 }
 
 template <typename T>
-int launch_pack(GpuContext *ctx, T *dst, const uint64_t *src, size_t words, bool bitrev) {
+int launch_pack(GpuContext *ctx, T *dst, const uint64_t *src, size_t words, bool bitrev, uint32_t limbs) {
     const unsigned threads = 256, grid = stride_grid(ctx, words, threads);
+    const auto *lc = (const gp::LimbConst<T> *)ctx->d_limb;
     if (bitrev)
-        gp::pack_kernel<T, uint64_t, true><<<grid, threads, 0, gp::cur(ctx)>>>(dst, src, words, (uint32_t)ctx->logN);
+        gp::pack_kernel<T, uint64_t, true><<<grid, threads, 0, gp::cur(ctx)>>>(dst, src, words, (uint32_t)ctx->logN, 0, limbs, lc);
     else
-        gp::pack_kernel<T, uint64_t, false><<<grid, threads, 0, gp::cur(ctx)>>>(dst, src, words, (uint32_t)ctx->logN);
+        gp::pack_kernel<T, uint64_t, false><<<grid, threads, 0, gp::cur(ctx)>>>(dst, src, words, (uint32_t)ctx->logN, 0, limbs, lc);
     gp::count_launch();
     GP_CHECK_LAUNCH("pack_kernel");
     return 0;
@@ -83,7 +84,7 @@ extern "C" int gpu_matrix_load_rns_batch(GpuMatrix *mat, const uint8_t *bytes, s
                 "cudaMemcpy2DAsync(H2D)");
     const size_t words = polys * mat->poly_words();
     const bool bitrev = format == GPU_POLY_FORMAT_EVAL;
-    int st = GP_DISPATCH_WIDTH(ctx, return launch_pack<T>(ctx, (T *)mat->data, (const uint64_t *)stage.p, words, bitrev););
+    int st = GP_DISPATCH_WIDTH(ctx, return launch_pack<T>(ctx, (T *)mat->data, (const uint64_t *)stage.p, words, bitrev, (uint32_t)mat->limbs()););
     if (st) return st;
     mat->format = format;  // MatrixSerde.cu:739
     return make_event_set(ctx, out_events);

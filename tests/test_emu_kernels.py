@@ -34,6 +34,8 @@ def emu():
     lib.emu_set_fuse_top.argtypes = [C.c_int]
     lib.emu_set_fuse_top.restype = None
     lib.emu_f64_blocks.restype = C.c_size_t
+    lib.emu_set_cluster.argtypes = [C.c_int]
+    lib.emu_set_cluster.restype = None
     lib.emu_matmul.argtypes = [C.c_int, C.c_int, C.c_uint32, u64p, u64p, u64p, u64p] + [C.c_uint32] * 8 + [C.c_int]
     return lib
 
@@ -363,3 +365,67 @@ def test_emu_matmul_worst_case_accumulation(emu):
         out = np.zeros_like(want)
         assert emu.emu_matmul(0, n.bit_length() - 1, 1, p(mod), p(out), p(A), p(B), 1, k, 4, 4, 0, 4, 0, 0, 0) == 0
         assert np.array_equal(out, want)
+
+
+# ---- cluster / DSMEM kernels (ntt_cluster.cuh): rings of 2, 4, 8 blocks ------------------------------------------------
+# With the cluster path on (the launcher's default) the ring goes through push -> local (forward) and local -> pull
+# (inverse) phases; with it off, through the round-1 global passes + block kernel.  Both must equal the oracle.
+CLUSTER_CASES = [
+    # (n, depth, bits, f64)
+    (1 << 15, 2, 28, 0),   # u32, 2 blocks of 2^14
+    (1 << 15, 1, 24, 0),   # NOCSUB
+    (1 << 16, 1, 29, 0),   # 4 blocks
+    (1 << 17, 1, 26, 0),   # 8 blocks, NOCSUB
+    (1 << 14, 2, 61, 0),   # u64 integer, 2 blocks of 2^13
+    (1 << 15, 1, 55, 0),   # u64 integer NOCSUB, 4 blocks
+    (1 << 16, 1, 59, 0),   # 8 blocks
+    (1 << 14, 2, 51, 1),   # FP64-pipe butterflies
+    (1 << 15, 1, 51, 1),
+    (1 << 16, 1, 45, 1),
+]
+
+
+@pytest.mark.parametrize("n,depth,bits,f64", CLUSTER_CASES)
+def test_emu_cluster_ntt_matches_oracle_and_global_pass_path(emu, n, depth, bits, f64):
+    pl = plan(n, depth, bits)
+    mod = np.array(pl.moduli, dtype=np.uint64)
+    logn = n.bit_length() - 1
+    a = pl.uniform(1, 2, seed=31 + n)
+    a[0, 1, :, : n // 2] = (mod - 1)[:, None]  # half of one polynomial at the largest residue
+    want = to_dev(pl.ntt(a))
+    emu.emu_set_f64(f64)
+    try:
+        before = emu.emu_f64_blocks()
+        for cluster in (1, 0):
+            emu.emu_set_cluster(cluster)
+            d = a.copy()
+            assert emu.emu_ntt(0, logn, depth, p(mod), p(d), 2, 0, 0) == 0
+            assert np.array_equal(d, want), f"forward, cluster={cluster}"
+            assert emu.emu_ntt(0, logn, depth, p(mod), p(d), 2, 1, 0) == 0
+            assert np.array_equal(d, a), f"inverse, cluster={cluster}"
+        if f64:
+            assert emu.emu_f64_blocks() > before
+    finally:
+        emu.emu_set_cluster(1)
+        emu.emu_set_f64(0)
+
+
+@pytest.mark.parametrize("n,depth,bits,bb,small,f64", [(1 << 15, 2, 28, 14, 0, 0), (1 << 15, 1, 24, 12, 1, 0), (1 << 16, 1, 28, 10, 0, 0),
+                                                     (1 << 14, 2, 51, 17, 0, 1), (1 << 15, 1, 51, 17, 0, 1), (1 << 14, 1, 61, 21, 0, 0)])
+def test_emu_cluster_decompose_matches_oracle(emu, n, depth, bits, bb, small, f64):
+    pl = plan(n, depth, bits)
+    mod = np.array(pl.moduli, dtype=np.uint64)
+    rows, cols = 1, 3
+    src = pl.uniform(rows, cols, seed=9)
+    full = to_dev(pl.ntt(pl.decompose(src, bb, bool(small))))
+    ell = pl.ell(bb, bool(small))
+    emu.emu_set_f64(f64)
+    try:
+        for cluster in (1, 0):
+            emu.emu_set_cluster(cluster)
+            out = np.zeros((rows * ell, 2, depth, n), dtype=np.uint64)
+            assert emu.emu_decompose(0, n.bit_length() - 1, depth, p(mod), p(src), rows, cols, 1, 2, bb, small, 1, p(out), 0) == 0
+            assert np.array_equal(out, np.ascontiguousarray(full[:, 1:3])), f"cluster={cluster}"
+    finally:
+        emu.emu_set_cluster(1)
+        emu.emu_set_f64(0)
