@@ -318,13 +318,7 @@ GP_HD typename DigitSrcOf<T>::type make_digit_src(const T *__restrict__ src, con
     }
 }
 
-// ---- launch shape ---------------------------------------------------------------------------------------------------
-// (block, cluster) split of a ring of 2^logn words: 64 KB blocks (2^14 u32 / 2^13 u64 words), cluster of at most 8
-template <typename T> inline int cluster_block_log() { return sizeof(T) == 4 ? 14 : 13; }
-template <typename T> inline int cluster_log(int logn) {
-    const int lc = logn - cluster_block_log<T>();
-    return (lc >= 1 && lc <= 3) ? lc : 0;
-}
+// launch shape: cluster_block_log / cluster_log live in ntt_fast.cuh (host planning code uses them without this header)
 
 #if defined(__CUDACC__) && !defined(GP_EMU_BUILD)  // the kernels proper (emu.cu drives the phases above on the host)
 template <typename T, int LOGB, int LC, bool NOCSUB, class Src>

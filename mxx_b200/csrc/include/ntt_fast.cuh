@@ -653,6 +653,14 @@ template <typename T> inline int fast_block_log(int logn) {
     const int cap = sizeof(T) == 4 ? 15 : 14;
     return logn <= cap ? logn : cap - 1;
 }
+// ---- launch shape of the cluster kernels (ntt_cluster.cuh) ---------------------------------------------------------------------------------------------------
+// (block, cluster) split of a ring of 2^logn words: 64 KB blocks (2^14 u32 / 2^13 u64 words), cluster of at most 8
+template <typename T> inline int cluster_block_log() { return sizeof(T) == 4 ? 14 : 13; }
+template <typename T> inline int cluster_log(int logn) {
+    const int lc = logn - cluster_block_log<T>();
+    return (lc >= 1 && lc <= 3) ? lc : 0;
+}
+
 template <typename T, int LOGB, bool NOCSUB>
 GP_HD void fast_fwd_cta(uint32_t bid, void *smem, const T *src, T *dst, uint32_t limbs, uint32_t logn,
                         const TwPair<T> *__restrict__ tw_all, const LimbConst<T> *__restrict__ lc) {

@@ -1,0 +1,5 @@
+// MatrixArith.cu — one translation unit of the matrix layer (see Matrix.cu for the list and MatrixShared.cuh for what crosses units).
+#include "MatrixShared.cuh"
+
+#include "MatrixCommon.inl"
+#include "MatrixArith.inl"

@@ -66,8 +66,10 @@ int launch_matmul_f64_tile(GpuContext *ctx, uint64_t *out, const uint64_t *A, co
     });
 }
 
+}  // namespace
+
 // out[:, out_col0 : out_col0+cols] = A(rows x inner) * B[:, b_col0 : b_col0+cols]
-template <typename T> int run_matmul(GpuContext *ctx, T *out, const T *A, const T *B, gp::MatmulGeom g) {
+template <typename T> int gpm::run_matmul(GpuContext *ctx, T *out, const T *A, const T *B, gp::MatmulGeom g) {
     if (g.rows == 0 || g.cols == 0 || g.limbs == 0) return 0;
     g.logn = (uint32_t)ctx->logN;
     g.fold = ctx->mac_fold;
@@ -100,12 +102,14 @@ template <typename T> int run_matmul(GpuContext *ctx, T *out, const T *A, const 
     return launch_matmul_tile<T, VMAX, 1, 1, 6, 128>(ctx, out, A, B, g);
 }
 
-int binary_check(const char *name, GpuMatrix *out, const GpuMatrix *lhs, const GpuMatrix *rhs) {
+template int gpm::run_matmul<uint32_t>(GpuContext *, uint32_t *, const uint32_t *, const uint32_t *, gp::MatmulGeom);
+template int gpm::run_matmul<uint64_t>(GpuContext *, uint64_t *, const uint64_t *, const uint64_t *, gp::MatmulGeom);
+
+int gpm::binary_check(const char *name, GpuMatrix *out, const GpuMatrix *lhs, const GpuMatrix *rhs) {
     if (!out || !lhs || !rhs) return gp::set_error(std::string("invalid ") + name + " arguments");
     if (!same_ctx(out, lhs) || !same_ctx(out, rhs)) return gp::set_error(std::string("context mismatch in ") + name);
     return 0;
 }
-}  // namespace
 
 extern "C" int gpu_matrix_add(GpuMatrix *out, const GpuMatrix *lhs, const GpuMatrix *rhs) {
     if (binary_check("gpu_matrix_add", out, lhs, rhs)) return 1;

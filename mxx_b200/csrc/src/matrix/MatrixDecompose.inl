@@ -83,30 +83,6 @@ template <typename T> int dispatch_fast_decompose(GpuContext *ctx, const T *src,
     }
 }
 
-template <typename K, int LOGB, int LC, bool NOCSUB>
-int launch_cluster_decompose(GpuContext *ctx, const K *src, K *out, const gp::DecompGeom &g, size_t opl) {
-    static std::atomic<uint32_t> done{0};
-    constexpr size_t smem = gp::fast_smem_bytes<K, LOGB>();
-    auto kernel = gp::fast_decompose_cluster_kernel<K, LOGB, LC, NOCSUB>;
-    if (optin_smem(kernel, smem, ctx->device, done)) return 1;
-    kernel<<<(unsigned)(opl << LC), gp::FastCfg<K, LOGB>::kThreads, smem, gp::cur(ctx)>>>(src, out, g, fwd_tab<K>(ctx), limb_tab<K>(ctx));
-    gp::count_launch();
-    GP_CHECK_LAUNCH("fast_decompose_cluster_kernel");
-    return 0;
-}
-template <typename K> int dispatch_cluster_decompose(GpuContext *ctx, const K *src, K *out, const gp::DecompGeom &g, size_t opl, int lc) {
-    constexpr int LB = sizeof(K) == 4 ? 14 : 13;
-    if constexpr (gp::is_f64<K>::value) {
-#define GP_CALL(LC) launch_cluster_decompose<K, LB, LC, false>(ctx, src, out, g, opl)
-        GP_CLUSTER_SWITCH(lc, GP_CALL)
-#undef GP_CALL
-    } else {
-#define GP_CALL(LC) (ctx->nocsub ? launch_cluster_decompose<K, LB, LC, true>(ctx, src, out, g, opl) : launch_cluster_decompose<K, LB, LC, false>(ctx, src, out, g, opl))
-        GP_CLUSTER_SWITCH(lc, GP_CALL)
-#undef GP_CALL
-    }
-}
-
 // out (rows*ell x cols) <- digits of src[:, src_col0 : src_col0 + cols] (src in COEFF form)
 template <typename T>
 int run_decompose(GpuContext *ctx, const T *src_coeff, T *out, size_t rows, size_t src_cols, size_t src_col0, size_t cols,
@@ -123,10 +99,7 @@ int run_decompose(GpuContext *ctx, const T *src_coeff, T *out, size_t rows, size
     const size_t opl = rows * g.ell * cols * limbs;
     if (opl == 0) return 0;
     if (const int lc = ntt_cluster_log<T>(ctx); to_eval && lc > 0) {  // rings of 2..8 blocks: digits extracted by the cluster's push phase
-        if constexpr (sizeof(T) == 8) {
-            if (ctx->f64_ntt) return dispatch_cluster_decompose<gp::F64>(ctx, (const gp::F64 *)src_coeff, (gp::F64 *)out, g, opl, lc);
-        }
-        return dispatch_cluster_decompose<T>(ctx, src_coeff, out, g, opl, lc);
+        return gpm::run_cluster_decompose<T>(ctx, src_coeff, out, g, opl, lc);
     }
     const int logn = ctx->logN, logb = ntt_block_log<T>(ctx), top = logn - logb;
     if (to_eval && top == 0 && use_fast<T>(ctx, logb)) {
@@ -136,7 +109,13 @@ int run_decompose(GpuContext *ctx, const T *src_coeff, T *out, size_t rows, size
         return dispatch_fast_decompose<T>(ctx, src_coeff, out, g, (unsigned)opl, logb);
     }
     const size_t smem = gp::ntt_smem_bytes<T>(logb);
-    if (ensure_ntt_smem<T>(ctx, smem)) return 1;
+    {  // > 48 KB dynamic shared memory for this translation unit's runtime-planned decomposition kernels
+        static std::atomic<uint32_t> done_e{0}, done_c{0};
+        if ((int)smem > ctx->max_smem_optin) return gp::set_error("NTT block does not fit shared memory on this device");
+        if (smem > 48 * 1024 && (optin_smem(gp::decompose_kernel<T, true>, (size_t)ctx->max_smem_optin, ctx->device, done_e) ||
+                                 optin_smem(gp::decompose_kernel<T, false>, (size_t)ctx->max_smem_optin, ctx->device, done_c)))
+            return 1;
+    }
     const auto *tw = (const gp::TwPair<T> *)ctx->d_fwd;
     const auto *lc = (const gp::LimbConst<T> *)ctx->d_limb;
     const unsigned grid = (unsigned)(opl << top), threads = gp::NttCfg<T>::kThreads;

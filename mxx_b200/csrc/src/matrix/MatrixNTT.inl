@@ -6,42 +6,6 @@
 
 namespace {
 
-// block (per-CTA) size: the compile-time-planned kernels of ntt_fast.cuh when one exists for this
-// ring, else the generic kernel of ntt.cuh
-template <typename T> inline int ntt_block_log(const GpuContext *ctx) {
-    const int fb = gp::fast_block_log<T>(ctx->logN);
-    if (!ctx->force_generic_ntt && ctx->ntt_block_override >= 12 && ctx->ntt_block_override < ctx->logN &&
-        gp::fast_supported<T>(ctx->ntt_block_override))
-        return ctx->ntt_block_override;  // MXX_NTT_BLOCK_LOG: tuning knob for rings above one CTA's shared memory
-    if (!ctx->force_generic_ntt && gp::fast_supported<T>(fb)) return fb;
-    return gp::ntt_block_log<T>(ctx->logN);
-}
-template <typename T> inline bool use_fast(const GpuContext *ctx, int logb) {
-    return !ctx->force_generic_ntt && gp::fast_supported<T>(logb) && logb == ntt_block_log<T>(ctx);
-}
-using gp::split_top;
-
-// device tables by working type: the F64 kernels have their own (Runtime.cu upload_tables)
-template <typename T> inline const gp::TwPair<T> *fwd_tab(const GpuContext *c) {
-    return (const gp::TwPair<T> *)(gp::is_f64<T>::value ? c->d_fwd_f64 : c->d_fwd);
-}
-template <typename T> inline const gp::TwPair<T> *inv_tab(const GpuContext *c) {
-    return (const gp::TwPair<T> *)(gp::is_f64<T>::value ? c->d_inv_f64 : c->d_inv);
-}
-template <typename T> inline const gp::LimbConst<T> *limb_tab(const GpuContext *c) {
-    return (const gp::LimbConst<T> *)(gp::is_f64<T>::value ? c->d_limb_f64 : c->d_limb);
-}
-
-// opt-in to > 48 KB of dynamic shared memory, once per kernel instantiation and device
-template <typename K> int optin_smem(K kernel, size_t bytes, int device, std::atomic<uint32_t> &done) {
-    if (bytes <= 48 * 1024) return 0;
-    const uint32_t bit = 1u << (device & 31);
-    if (done.load(std::memory_order_acquire) & bit) return 0;
-    GP_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes), "cudaFuncSetAttribute");
-    done.fetch_or(bit, std::memory_order_release);
-    return 0;
-}
-
 template <typename T, int LOGB, bool NOCSUB>
 int launch_fast_fwd(GpuContext *ctx, const T *src, T *dst, unsigned grid, uint32_t limbs) {
     static std::atomic<uint32_t> done{0};
@@ -66,16 +30,6 @@ int launch_fast_inv(GpuContext *ctx, const T *src, T *dst, unsigned grid, uint32
     GP_CHECK_LAUNCH("fast_ntt_inv_kernel");
     return 0;
 }
-#define GP_FAST_LOGB_SWITCH(logb, CALL)                                   \
-    switch (logb) {                                                       \
-        case 12: return CALL(12);                                         \
-        case 13: return CALL(13);                                         \
-        case 14: return CALL(14);                                         \
-        case 15:                                                          \
-            if constexpr (sizeof(T) == 4) return CALL(15);                \
-            [[fallthrough]];                                              \
-        default: return gp::set_error("no compile-time NTT plan for this block size"); \
-    }
 template <typename T> int dispatch_fast_fwd(GpuContext *ctx, const T *src, T *dst, unsigned grid, uint32_t limbs, int logb) {
     if constexpr (gp::is_f64<T>::value) {
 #define GP_CALL(LB) launch_fast_fwd<T, LB, false>(ctx, src, dst, grid, limbs)
@@ -93,72 +47,14 @@ template <typename T> int dispatch_fast_inv(GpuContext *ctx, const T *src, T *ds
 #undef GP_CALL
 }
 
-// ---- cluster / DSMEM kernels (ntt_cluster.cuh): rings of 2, 4 or 8 shared-memory blocks in ONE pass over HBM ----
-// log2(cluster size) for this context's ring, 0 = not applicable (ring fits one block, knobs, ring too large)
-template <typename T> inline int ntt_cluster_log(const GpuContext *ctx) {
-    if (!ctx->ntt_cluster || ctx->force_generic_ntt || ctx->ntt_block_override) return 0;
-    return gp::cluster_log<T>(ctx->logN);
-}
-template <typename K, int LOGB, int LC, bool NOCSUB>
-int launch_cluster_fwd(GpuContext *ctx, const K *src, K *dst, size_t pl, uint32_t limbs) {
-    static std::atomic<uint32_t> done{0};
-    constexpr size_t smem = gp::fast_smem_bytes<K, LOGB>();
-    auto kernel = gp::fast_ntt_fwd_cluster_kernel<K, LOGB, LC, NOCSUB>;
-    if (optin_smem(kernel, smem, ctx->device, done)) return 1;
-    kernel<<<(unsigned)(pl << LC), gp::FastCfg<K, LOGB>::kThreads, smem, gp::cur(ctx)>>>(src, dst, limbs, fwd_tab<K>(ctx), limb_tab<K>(ctx));
-    gp::count_launch();
-    GP_CHECK_LAUNCH("fast_ntt_fwd_cluster_kernel");
-    return 0;
-}
-template <typename K, int LOGB, int LC>
-int launch_cluster_inv(GpuContext *ctx, const K *src, K *dst, size_t pl, uint32_t limbs) {
-    static std::atomic<uint32_t> done{0};
-    constexpr size_t smem = gp::fast_smem_bytes<K, LOGB>();
-    auto kernel = gp::fast_ntt_inv_cluster_kernel<K, LOGB, LC>;
-    if (optin_smem(kernel, smem, ctx->device, done)) return 1;
-    kernel<<<(unsigned)(pl << LC), gp::FastCfg<K, LOGB>::kThreads, smem, gp::cur(ctx)>>>(src, dst, limbs, inv_tab<K>(ctx), limb_tab<K>(ctx));
-    gp::count_launch();
-    GP_CHECK_LAUNCH("fast_ntt_inv_cluster_kernel");
-    return 0;
-}
-#define GP_CLUSTER_SWITCH(lc, CALL)                                                     \
-    switch (lc) {                                                                       \
-        case 1: return CALL(1);                                                         \
-        case 2: return CALL(2);                                                         \
-        case 3: return CALL(3);                                                         \
-        default: return gp::set_error("no cluster NTT plan for this ring size");        \
-    }
-// K = the kernels' working type: T, or gp::F64 over u64 words
-template <typename K> int dispatch_cluster_fwd(GpuContext *ctx, const K *src, K *dst, size_t pl, uint32_t limbs, int lc) {
-    constexpr int LB = sizeof(K) == 4 ? 14 : 13;
-    if constexpr (gp::is_f64<K>::value) {
-#define GP_CALL(LC) launch_cluster_fwd<K, LB, LC, false>(ctx, src, dst, pl, limbs)
-        GP_CLUSTER_SWITCH(lc, GP_CALL)
-#undef GP_CALL
-    } else {
-#define GP_CALL(LC) (ctx->nocsub ? launch_cluster_fwd<K, LB, LC, true>(ctx, src, dst, pl, limbs) : launch_cluster_fwd<K, LB, LC, false>(ctx, src, dst, pl, limbs))
-        GP_CLUSTER_SWITCH(lc, GP_CALL)
-#undef GP_CALL
-    }
-}
-template <typename K> int dispatch_cluster_inv(GpuContext *ctx, const K *src, K *dst, size_t pl, uint32_t limbs, int lc) {
-    constexpr int LB = sizeof(K) == 4 ? 14 : 13;
-#define GP_CALL(LC) launch_cluster_inv<K, LB, LC>(ctx, src, dst, pl, limbs)
-    GP_CLUSTER_SWITCH(lc, GP_CALL)
-#undef GP_CALL
-}
-
+// opt in to > 48 KB dynamic shared memory for the runtime-planned kernels of ntt.cuh (once per device; the
+// decomposition kernels of the same family are configured by their own translation unit, MatrixDecompose.inl)
 template <typename T> int ensure_ntt_smem(GpuContext *ctx, size_t bytes) {
-    // opt in to > 48 KB dynamic shared memory once per context and kernel family
-    if (bytes <= 48 * 1024 || ctx->smem_configured) return 0;
+    static std::atomic<uint32_t> done_f{0}, done_i{0};
+    if (bytes <= 48 * 1024) return 0;
     if ((int)bytes > ctx->max_smem_optin) return gp::set_error("NTT block does not fit shared memory on this device");
-    const int b = ctx->max_smem_optin;
-    GP_CUDA(cudaFuncSetAttribute(gp::ntt_fwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, b), "cudaFuncSetAttribute");
-    GP_CUDA(cudaFuncSetAttribute(gp::ntt_inv_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, b), "cudaFuncSetAttribute");
-    GP_CUDA(cudaFuncSetAttribute(gp::decompose_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, b), "cudaFuncSetAttribute");
-    GP_CUDA(cudaFuncSetAttribute(gp::decompose_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, b), "cudaFuncSetAttribute");
-    ctx->smem_configured = true;
-    return 0;
+    if (optin_smem(gp::ntt_fwd_kernel<T>, (size_t)ctx->max_smem_optin, ctx->device, done_f)) return 1;
+    return optin_smem(gp::ntt_inv_kernel<T>, (size_t)ctx->max_smem_optin, ctx->device, done_i);
 }
 
 template <typename T, int LOGR>
@@ -205,17 +101,16 @@ int dispatch_inv_global(GpuContext *ctx, T *d, size_t pl, uint32_t limbs, uint32
     }
 }
 
+}  // namespace
+
 // dst = NTT(src) for `polys` polynomials of `limbs` limbs each (src may equal dst).
 // first_top_pass_done: the caller already ran the first global pass (fused with its producer, MatrixDecompose.inl).
 template <typename T>
-int run_ntt_fwd(GpuContext *ctx, const T *src, T *dst, size_t polys, uint32_t limbs, bool first_top_pass_done = false) {
+int gpm::run_ntt_fwd(GpuContext *ctx, const T *src, T *dst, size_t polys, uint32_t limbs, bool first_top_pass_done) {
     const size_t pl = polys * limbs;
     if (pl == 0) return 0;
     if (const int lc = ntt_cluster_log<T>(ctx); lc > 0 && !first_top_pass_done) {
-        if constexpr (sizeof(T) == 8) {
-            if (ctx->f64_ntt) return dispatch_cluster_fwd<gp::F64>(ctx, (const gp::F64 *)src, (gp::F64 *)dst, pl, limbs, lc);
-        }
-        return dispatch_cluster_fwd<T>(ctx, src, dst, pl, limbs, lc);
+        return gpm::run_cluster_fwd<T>(ctx, src, dst, pl, limbs, lc);
     }
     const int logn = ctx->logN, logb = ntt_block_log<T>(ctx), top = logn - logb;
     const bool fast = use_fast<T>(ctx, logb);
@@ -247,14 +142,11 @@ int run_ntt_fwd(GpuContext *ctx, const T *src, T *dst, size_t polys, uint32_t li
     return 0;
 }
 
-template <typename T> int run_ntt_inv(GpuContext *ctx, const T *src, T *dst, size_t polys, uint32_t limbs) {
+template <typename T> int gpm::run_ntt_inv(GpuContext *ctx, const T *src, T *dst, size_t polys, uint32_t limbs) {
     const size_t pl = polys * limbs;
     if (pl == 0) return 0;
     if (const int lc = ntt_cluster_log<T>(ctx); lc > 0) {
-        if constexpr (sizeof(T) == 8) {
-            if (ctx->f64_ntt) return dispatch_cluster_inv<gp::F64>(ctx, (const gp::F64 *)src, (gp::F64 *)dst, pl, limbs, lc);
-        }
-        return dispatch_cluster_inv<T>(ctx, src, dst, pl, limbs, lc);
+        return gpm::run_cluster_inv<T>(ctx, src, dst, pl, limbs, lc);
     }
     const int logn = ctx->logN, logb = ntt_block_log<T>(ctx), top = logn - logb;
     const bool fast = use_fast<T>(ctx, logb);
@@ -287,7 +179,12 @@ template <typename T> int run_ntt_inv(GpuContext *ctx, const T *src, T *dst, siz
     return 0;
 }
 
-int matrix_transform(GpuMatrix *mat, bool inverse) {
+template int gpm::run_ntt_fwd<uint32_t>(GpuContext *, const uint32_t *, uint32_t *, size_t, uint32_t, bool);
+template int gpm::run_ntt_fwd<uint64_t>(GpuContext *, const uint64_t *, uint64_t *, size_t, uint32_t, bool);
+template int gpm::run_ntt_inv<uint32_t>(GpuContext *, const uint32_t *, uint32_t *, size_t, uint32_t);
+template int gpm::run_ntt_inv<uint64_t>(GpuContext *, const uint64_t *, uint64_t *, size_t, uint32_t);
+
+int gpm::matrix_transform(GpuMatrix *mat, bool inverse) {
     GpuContext *ctx = mat->ctx;
     if (mat->polys() == 0 || mat->level < 0) {
         mat->format = inverse ? GPU_POLY_FORMAT_COEFF : GPU_POLY_FORMAT_EVAL;
@@ -302,7 +199,6 @@ int matrix_transform(GpuMatrix *mat, bool inverse) {
     mat->format = inverse ? GPU_POLY_FORMAT_COEFF : GPU_POLY_FORMAT_EVAL;
     return 0;
 }
-}  // namespace
 
 extern "C" int gpu_matrix_ntt_all(GpuMatrix *mat) {
     if (!mat || !mat->ctx) return gp::set_error("invalid gpu_matrix_ntt_all arguments");
