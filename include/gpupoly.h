@@ -128,6 +128,20 @@ int gpu_matrix_sample_distribution_columns(GpuMatrix *out, int dist_type, double
  * (src/matrix/gpu_dcrt_poly.rs:1414-1493).  lhs EVAL; rhs EVAL or COEFF; out EVAL.
  * small != 0 selects mul_decompose_small (gpu_dcrt_poly.rs:1495-1574). */
 int gpu_matrix_mul_decompose(GpuMatrix *out, const GpuMatrix *lhs, const GpuMatrix *rhs, uint32_t base_bits, int small);
+/* The same product for a LIMB-SHARDED job (SURVEY.md 8e "Alternative (limbs)"; the reference has only the scaffold,
+ * cuda/src/Runtime.cu:254-280, and rejects it at run time, cuda/src/matrix/MatrixNTT.cu:495-498).  out and lhs live in a
+ * context whose moduli are this GPU's subset of the CRT basis; other_coeff is the coefficient-form right operand (d x c)
+ * with ALL `towers` towers of the basis as an all-gather of the ranks' [poly][towers_per_group][n] blocks leaves it:
+ * tower t of polynomial p at (t / towers_per_group) * group_stride_words + p * poly_stride_words + (t % towers_per_group) * n
+ * words of this context's storage width.  out(r x out_cols) = lhs(r x d*ell) * G^-1(other[:, col0 : col0 + out_cols]) on this
+ * context's limbs; ell follows the FULL basis (tower_moduli). */
+int gpu_matrix_mul_decompose_gathered(GpuMatrix *out, const GpuMatrix *lhs, const void *other_coeff, size_t d, size_t c, size_t col0,
+                                      const uint64_t *tower_moduli, size_t towers, size_t towers_per_group,
+                                      size_t group_stride_words, size_t poly_stride_words, uint32_t base_bits, int small);
+/* out[dst block] += src[src block] * scalar (scalar 1x1; all EVAL): the `+ c_y * x` tail of a BGG encoding product
+ * (src/bgg/encoding.rs:135) applied in place to the vector rows of a stacked product, one launch. */
+int gpu_matrix_add_scaled_block(GpuMatrix *out, const GpuMatrix *src, const GpuMatrix *scalar, size_t dst_row, size_t dst_col,
+                                size_t src_row, size_t src_col, size_t rows, size_t cols);
 /* Big-integer coefficients <-> residues ON THE DEVICE: the conversion step either side of the path
  * (SURVEY 8f-4).  words[(poly * n + j) * words_per_coeff + w], little-endian u64 words of the coefficient.
  * load: every active limb receives the coefficient mod q_limb — the host BigUint `%` loop of

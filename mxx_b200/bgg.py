@@ -79,6 +79,23 @@ def encode(secret: GpuDCRTPolyMatrix, pubkey: BggPublicKey, plaintext: GpuDCRTPo
     return BggEncoding(vec, pubkey, plaintext)
 
 
+class StackedEncoding:
+    """A BGG+ encoding kept as ONE (1 + d) x m matrix [c ; A] (vector row(s) on top of the public key) plus its plaintext:
+    the layout a product chain wants, because the stacked matrix IS the left operand of the next fused product — no
+    concat before and no slices after each gate."""
+
+    def __init__(self, stacked: GpuDCRTPolyMatrix, vec_rows: int, plaintext: GpuDCRTPolyMatrix | None):
+        self.stacked, self.vec_rows, self.plaintext = stacked, int(vec_rows), plaintext
+
+    @classmethod
+    def from_encoding(cls, enc: BggEncoding) -> "StackedEncoding":
+        return cls(enc.vector.concat_rows([enc.pubkey.matrix]), enc.vector.nrow, enc.plaintext)
+
+    def to_encoding(self) -> BggEncoding:
+        s = self.stacked
+        return BggEncoding(s.slice_rows(0, self.vec_rows), BggPublicKey(s.slice_rows(self.vec_rows, s.nrow)), self.plaintext)
+
+
 class ShardedBggEvaluator:
     """Chain of encoding products with right operands sharded by columns over the ranks."""
 
@@ -89,13 +106,36 @@ class ShardedBggEvaluator:
                  right_plaintext: GpuDCRTPolyMatrix | None, ncol: int) -> BggEncoding:
         """left: whole encoding (replicated); right_*_local: this rank's columns of c_y and A_y.
         Returns the whole product encoding on every rank (one all-gather of the stacked (1+d) x m block)."""
+        return self.mul_gate_stacked(StackedEncoding.from_encoding(left), right_vec_local, right_pk_local, right_plaintext, ncol).to_encoding()
+
+    def mul_gate_stacked(self, left: StackedEncoding, right_vec_local: GpuDCRTPolyMatrix, right_pk_local: GpuDCRTPolyMatrix,
+                         right_plaintext: GpuDCRTPolyMatrix | None, ncol: int) -> StackedEncoding:
+        """The same gate on stacked encodings: one fused mul_decompose on the local columns (no collective), the
+        `+ c_y * x` tail applied in place to the vector rows (one launch), one in-place all-gather per row."""
         if left.plaintext is None:
             raise ValueError("Unknown plaintext for the left-hand input of multiplication")
-        stacked = left.vector.concat_rows([left.pubkey.matrix])
-        prod_local = self.ops.mul_decompose(stacked, right_pk_local)                       # no collective
-        vec_rows = left.vector.nrow
-        first = prod_local.slice_rows(0, vec_rows) + right_vec_local.mul_scalar(left.plaintext)
-        local = first.concat_rows([prod_local.slice_rows(vec_rows, prod_local.nrow)])
-        full = self.ops.all_gather_columns(local, ncol)                                    # the exchange step
+        prod_local = self.ops.mul_decompose(left.stacked, right_pk_local)                   # no collective
+        prod_local.add_scaled_block_from(right_vec_local, left.plaintext, 0, 0, 0, 0, left.vec_rows, prod_local.ncol)
+        full = self.ops.all_gather_columns(prod_local, ncol)                               # the exchange step
         pt = left.plaintext * right_plaintext if right_plaintext is not None else None
-        return BggEncoding(full.slice_rows(0, vec_rows), BggPublicKey(full.slice_rows(vec_rows, full.nrow)), pt)
+        return StackedEncoding(full, left.vec_rows, pt)
+
+
+class GridBggEvaluator:
+    """The same chain on a 2-D (limb group x column block) partition (mxx_b200.dist.GridShardedOps).  Every matrix
+    holds this rank's limbs only; the left encoding has all m columns, the right operands this rank's column block.
+    Per gate: one all-gather of the coefficient-form A_y block along the limb axis (inside mul_decompose), the local
+    product, and — only when the columns are split too — one all-gather of the result rows along the column axis."""
+
+    def __init__(self, ops):
+        self.ops = ops
+
+    def mul_gate_stacked(self, left: StackedEncoding, right_vec_local: GpuDCRTPolyMatrix, right_pk_local: GpuDCRTPolyMatrix,
+                         right_plaintext: GpuDCRTPolyMatrix | None, ncol: int) -> StackedEncoding:
+        if left.plaintext is None:
+            raise ValueError("Unknown plaintext for the left-hand input of multiplication")
+        prod_local = self.ops.mul_decompose(left.stacked, right_pk_local)                   # limb-axis all-gather inside
+        prod_local.add_scaled_block_from(right_vec_local, left.plaintext, 0, 0, 0, 0, left.vec_rows, prod_local.ncol)
+        full = self.ops.all_gather_columns(prod_local, ncol)                               # column-axis all-gather
+        pt = left.plaintext * right_plaintext if right_plaintext is not None else None
+        return StackedEncoding(full, left.vec_rows, pt)

@@ -95,6 +95,26 @@ __global__ void add_rect_kernel(T *__restrict__ dst, const T *__restrict__ src, 
     }
 }
 
+// dst block += src block * scalar (one polynomial, EVAL); the tail of a BGG encoding product (src/bgg/encoding.rs:135)
+// applied in place to the rows of the stacked product that hold the vector part
+template <typename T, int V>
+__global__ void fma_rect_kernel(T *__restrict__ dst, const T *__restrict__ src, const T *__restrict__ scalar, RectGeom g, size_t total,
+                                uint32_t limbs, uint32_t logn, const LimbConst<T> *__restrict__ lc) {
+    const size_t step = (size_t)gridDim.x * GP_NT;
+    const size_t poly_words = (size_t)limbs << logn;
+    for (size_t i = (size_t)blockIdx.x * GP_NT + GP_TID; i < total; i += step) {
+        const size_t off = i * V, rp = off / poly_words, w = off % poly_words;
+        const size_t r = rp / g.cols, cc = rp % g.cols;
+        const LimbConst<T> c = lc[(uint32_t)(w >> logn)];
+        T *d = dst + ((g.dst_row + r) * g.dst_cols + g.dst_col + cc) * poly_words + w;
+        const T *s = src + ((g.src_row + r) * g.src_cols + g.src_col + cc) * poly_words + w;
+        Vec<T, V> x = ldv<T, V>(d), y = ldv<T, V>(s), z = ldv<T, V>(scalar + w);
+#pragma unroll
+        for (int k = 0; k < V; k++) x.v[k] = add_mod<T>(x.v[k], mul_mod<T>(y.v[k], z.v[k], c), c.q);
+        stv<T, V>(d, x);
+    }
+}
+
 // dst block = src block (backs copy, copy_block, slice, concat, entry; replaces
 // block_copy_rect_all_limbs_kernel, MatrixArith.cu:88)
 template <typename T, int V>

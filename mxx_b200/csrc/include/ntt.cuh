@@ -316,14 +316,60 @@ ntt_inv_kernel(const T *src, T *dst, uint32_t limbs, uint32_t logn, uint32_t log
 // Replaces memset + matrix_decompose_all_slots_kernel + a full NTT sweep
 // (cuda/src/matrix/MatrixDecompose.cu:1155-1161, 1240-1328).
 struct DecompGeom {
-    uint32_t limbs;      // active limbs of src/out
+    uint32_t limbs;      // active limbs of the OUTPUT (the limbs of the tables the kernel is given)
     uint32_t src_cols;   // columns of the source matrix
     uint32_t src_col0;   // first source column of this chunk
     uint32_t cols;       // columns of the output (chunk width)
-    uint32_t ell;        // digits per source poly in the output (dpt*limbs, or dpt if small)
+    uint32_t ell;        // digits per source poly in the output (dpt*towers, or dpt if small)
     uint32_t dpt;        // digits per tower
     uint32_t base_bits;
+    // Source addressing.  An ordinary matrix stores [poly][tower][n] with as many towers as the output has limbs
+    // (gathered == 0).  A LIMB-SHARDED caller (mxx_b200/dist.py, SURVEY 8e "Alternative (limbs)") hands over the
+    // coefficient-form source as all-gathered per-rank blocks [group][poly][towers_per_group][n]: tower t of source
+    // poly p then sits at (t / src_tpg) * src_group_stride + p * src_poly_stride + (t % src_tpg) * n words, and the
+    // towers' bit widths (the FULL basis, not the output's limbs) travel in tower_bits.
+    uint32_t gathered;
+    uint32_t src_tpg;
+    unsigned long long src_group_stride, src_poly_stride;
+    unsigned char tower_bits[64];
 };
+// Where one output (poly, limb) of a decomposition reads its digits: source offset (words), shift and bit count of the
+// digit (0 bits: the digit is zero), output limb.  Row order row*ell + t*dpt + dg with the narrowed last digit of a
+// tower (cuda/src/matrix/MatrixDecompose.cu:93-113).
+struct DigitSpec {
+    size_t soff;
+    uint32_t limb, shift, dbits;
+};
+template <typename LC>
+GP_HD DigitSpec digit_spec(const DecompGeom &g, size_t pl, uint32_t logn, const LC *__restrict__ lc) {
+    DigitSpec d;
+    d.limb = (uint32_t)(pl % g.limbs);
+    const size_t opoly = pl / g.limbs;
+    const size_t orow = opoly / g.cols, col = opoly % g.cols;
+    const size_t row = orow / g.ell;
+    const uint32_t loc = (uint32_t)(orow % g.ell), t = loc / g.dpt, dg = loc % g.dpt;
+    const size_t spoly = row * g.src_cols + g.src_col0 + col;
+    uint32_t sbits;
+    if (g.gathered) {
+        sbits = g.tower_bits[t & 63];
+        d.soff = (size_t)(t / g.src_tpg) * g.src_group_stride + spoly * g.src_poly_stride + ((size_t)(t % g.src_tpg) << logn);
+    } else {
+        sbits = lc[t].bits;
+        d.soff = (spoly * g.limbs + t) << logn;
+    }
+    d.shift = dg * g.base_bits;
+    d.dbits = 0;
+    if (d.shift < sbits) {
+        const uint32_t rem = sbits - d.shift;
+        d.dbits = g.base_bits < rem ? g.base_bits : rem;
+    }
+    return d;
+}
+template <typename T> GP_HD DigitSrc<T> make_int_digit_src(const T *__restrict__ src, const DigitSpec &d, T q, T one_s) {
+    constexpr uint32_t W = sizeof(T) * 8;
+    const T mask = d.dbits == 0 ? (T)0 : (d.dbits >= W ? ~(T)0 : (T)(((T)1 << d.dbits) - 1));
+    return DigitSrc<T>{src + d.soff, d.shift >= W ? 0u : d.shift, d.shift >= W ? (T)0 : mask, q, one_s};
+}
 template <typename T, bool TO_EVAL>
 GP_HD void decompose_cta(uint32_t bid, T *sm, const T *__restrict__ src, T *__restrict__ out, const DecompGeom &g,
                          uint32_t logn, uint32_t logb, const TwPair<T> *__restrict__ tw_all,
@@ -331,21 +377,12 @@ GP_HD void decompose_cta(uint32_t bid, T *sm, const T *__restrict__ src, T *__re
     const uint32_t lsub = logn - logb;
     const size_t pl = bid >> lsub;  // out (poly, limb)
     const uint32_t sb = bid & ((1u << lsub) - 1);
-    const uint32_t limb = (uint32_t)(pl % g.limbs);
-    const size_t opoly = pl / g.limbs;
-    const size_t orow = opoly / g.cols, col = opoly % g.cols;
-    const size_t row = orow / g.ell;
-    const uint32_t loc = (uint32_t)(orow % g.ell), t = loc / g.dpt, dg = loc % g.dpt;
+    const DigitSpec ds = digit_spec(g, pl, logn, lc);
+    const uint32_t limb = ds.limb;
     const LimbConst<T> c = lc[limb];
-    const uint32_t sbits = lc[t].bits, shift = dg * g.base_bits;
-    T mask = 0;
-    if (shift < sbits) {
-        const uint32_t rem = sbits - shift, db = g.base_bits < rem ? g.base_bits : rem;
-        mask = db >= sizeof(T) * 8 ? ~(T)0 : (T)(((T)1 << db) - 1);
-    }
-    const T *sp = src + (((row * g.src_cols + g.src_col0 + col) * g.limbs + t) << logn) + ((size_t)sb << logb);
     T *dp = out + (pl << logn) + ((size_t)sb << logb);
-    DigitSrc<T> dsrc{sp, shift >= sizeof(T) * 8 ? 0u : shift, shift >= sizeof(T) * 8 ? (T)0 : mask, c.q, c.one_s};
+    DigitSrc<T> dsrc = make_int_digit_src<T>(src, ds, c.q, c.one_s);
+    dsrc.p += (size_t)sb << logb;
     if (TO_EVAL) {
         fwd_block<T>(dsrc, dp, sm, logn, logb, sb, tw_all + ((size_t)limb << logn), c);
     } else {
@@ -400,20 +437,11 @@ GP_HD void decompose_fwd_global_cta(size_t bid, const T *__restrict__ src, T *__
     const uint32_t lg = logn - LOGR, stride = 1u << lg, lchunk = decompose_top_chunk_log<LOGR>(logn);
     const size_t pl = bid >> (lg - lchunk);  // out (poly, limb)
     const uint32_t e0 = (uint32_t)(bid & ((1u << (lg - lchunk)) - 1)) << lchunk;
-    const uint32_t limb = (uint32_t)(pl % g.limbs);
-    const size_t opoly = pl / g.limbs;
-    const size_t orow = opoly / g.cols, col = opoly % g.cols;
-    const size_t row = orow / g.ell;
-    const uint32_t loc = (uint32_t)(orow % g.ell), t = loc / g.dpt, dg = loc % g.dpt;
+    const DigitSpec ds = digit_spec(g, pl, logn, lc);
+    const uint32_t limb = ds.limb;
     const LimbConst<T> c = lc[limb];
-    const uint32_t sbits = lc[t].bits, shift = dg * g.base_bits;
-    T mask = 0;
-    if (shift < sbits) {
-        const uint32_t rem = sbits - shift, db = g.base_bits < rem ? g.base_bits : rem;
-        mask = db >= sizeof(T) * 8 ? ~(T)0 : (T)(((T)1 << db) - 1);
-    }
-    const T *sp = src + (((row * g.src_cols + g.src_col0 + col) * g.limbs + t) << logn) + e0;
-    DigitSrc<T> dsrc{sp, shift >= sizeof(T) * 8 ? 0u : shift, shift >= sizeof(T) * 8 ? (T)0 : mask, c.q, c.one_s};
+    DigitSrc<T> dsrc = make_int_digit_src<T>(src, ds, c.q, c.one_s);
+    dsrc.p += e0;
     const TwPair<T> *tw = tw_all + ((size_t)limb << logn);
     T *base = out + (pl << logn) + e0;
     for (uint32_t i = GP_TID; i < (1u << lchunk); i += GP_NT) {

@@ -294,27 +294,11 @@ template <> struct DigitSrcOf<F64> { typedef F64DigitSrc type; };
 template <typename T>
 GP_HD typename DigitSrcOf<T>::type make_digit_src(const T *__restrict__ src, const DecompGeom &g, size_t pl, uint32_t logn,
                                                   const LimbConst<T> *__restrict__ lc) {
-    const uint32_t limb = (uint32_t)(pl % g.limbs);
-    const size_t opoly = pl / g.limbs;
-    const size_t orow = opoly / g.cols, col = opoly % g.cols;
-    const size_t row = orow / g.ell;
-    const uint32_t loc = (uint32_t)(orow % g.ell), t = loc / g.dpt, dg = loc % g.dpt;
-    const uint32_t sbits = lc[t].bits, shift = dg * g.base_bits;
-    const size_t soff = ((row * g.src_cols + g.src_col0 + col) * g.limbs + t) << logn;
+    const DigitSpec ds = digit_spec(g, pl, logn, lc);
     if constexpr (is_f64<T>::value) {
-        uint64_t mask = 0;
-        if (shift < sbits) {
-            const uint32_t rem = sbits - shift, db = g.base_bits < rem ? g.base_bits : rem;
-            mask = db >= 64 ? ~0ULL : ((1ULL << db) - 1);
-        }
-        return F64DigitSrc{reinterpret_cast<const uint64_t *>(src + soff), shift >= 64 ? 0u : shift, shift >= 64 ? 0ULL : mask};
+        return make_f64_digit_src(src, ds);
     } else {
-        T mask = 0;
-        if (shift < sbits) {
-            const uint32_t rem = sbits - shift, db = g.base_bits < rem ? g.base_bits : rem;
-            mask = db >= sizeof(T) * 8 ? ~(T)0 : (T)(((T)1 << db) - 1);
-        }
-        return DigitSrc<T>{src + soff, shift >= sizeof(T) * 8 ? 0u : shift, shift >= sizeof(T) * 8 ? (T)0 : mask, lc[limb].q, lc[limb].one_s};
+        return make_int_digit_src<T>(src, ds, lc[ds.limb].q, lc[ds.limb].one_s);
     }
 }
 

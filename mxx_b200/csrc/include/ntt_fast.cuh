@@ -714,36 +714,24 @@ struct F64DigitSrc {
     uint64_t mask;
     GP_HD F64 operator()(uint32_t i) const { return F64{f64_from_word((p[i] >> shift) & mask)}; }  // source words < 2^51
 };
+GP_HD F64DigitSrc make_f64_digit_src(const F64 *__restrict__ src, const DigitSpec &d) {
+    const uint64_t mask = d.dbits == 0 ? 0ULL : (d.dbits >= 64 ? ~0ULL : ((1ULL << d.dbits) - 1));
+    return F64DigitSrc{reinterpret_cast<const uint64_t *>(src + d.soff), d.shift >= 64 ? 0u : d.shift, d.shift >= 64 ? 0ULL : mask};
+}
 // fused gadget decomposition + forward NTT (digit extraction is the load functor of pass 1);
 // geometry as decompose_cta in ntt.cuh, block = the whole transform (logn == LOGB)
 template <typename T, int LOGB, bool NOCSUB>
 GP_HD void fast_decompose_cta(uint32_t bid, void *smem, const T *__restrict__ src, T *__restrict__ out, const DecompGeom &g,
                               const TwPair<T> *__restrict__ tw_all, const LimbConst<T> *__restrict__ lc) {
     const size_t pl = bid;  // out (poly, limb)
-    const uint32_t limb = (uint32_t)(pl % g.limbs);
-    const size_t opoly = pl / g.limbs;
-    const size_t orow = opoly / g.cols, col = opoly % g.cols;
-    const size_t row = orow / g.ell;
-    const uint32_t loc = (uint32_t)(orow % g.ell), t = loc / g.dpt, dg = loc % g.dpt;
+    const DigitSpec ds = digit_spec(g, pl, LOGB, lc);
+    const uint32_t limb = ds.limb;
     const LimbConst<T> c = lc[limb];
-    const uint32_t sbits = lc[t].bits, shift = dg * g.base_bits;
     if constexpr (is_f64<T>::value) {
-        uint64_t mask = 0;
-        if (shift < sbits) {
-            const uint32_t rem = sbits - shift, db = g.base_bits < rem ? g.base_bits : rem;
-            mask = db >= 64 ? ~0ULL : ((1ULL << db) - 1);
-        }
-        const F64 *sp = src + (((row * g.src_cols + g.src_col0 + col) * g.limbs + t) << LOGB);
-        F64DigitSrc dsrc{reinterpret_cast<const uint64_t *>(sp), shift >= 64 ? 0u : shift, shift >= 64 ? 0ULL : mask};
+        const F64DigitSrc dsrc = make_f64_digit_src(src, ds);
         fast_fwd_block<T, LOGB, NOCSUB>(dsrc, out + (pl << LOGB), smem, LOGB, 0, tw_all + ((size_t)limb << LOGB), c);
     } else {
-        T mask = 0;
-        if (shift < sbits) {
-            const uint32_t rem = sbits - shift, db = g.base_bits < rem ? g.base_bits : rem;
-            mask = db >= sizeof(T) * 8 ? ~(T)0 : (T)(((T)1 << db) - 1);
-        }
-        const T *sp = src + (((row * g.src_cols + g.src_col0 + col) * g.limbs + t) << LOGB);
-        DigitSrc<T> dsrc{sp, shift >= sizeof(T) * 8 ? 0u : shift, shift >= sizeof(T) * 8 ? (T)0 : mask, c.q, c.one_s};
+        const DigitSrc<T> dsrc = make_int_digit_src<T>(src, ds, c.q, c.one_s);
         fast_fwd_block<T, LOGB, NOCSUB>(dsrc, out + (pl << LOGB), smem, LOGB, 0, tw_all + ((size_t)limb << LOGB), c);
     }
 }

@@ -301,7 +301,7 @@ int do_decompose(int logn, uint32_t limbs, const uint64_t *moduli, const uint64_
     uint64_t qmax = 0;
     for (uint32_t i = 0; i < limbs; i++) qmax = moduli[i] > qmax ? moduli[i] : qmax;
     const uint32_t crt_bits = 64 - (uint32_t)__builtin_clzll(qmax);
-    DecompGeom g;
+    DecompGeom g{};
     g.limbs = limbs;
     g.src_cols = (uint32_t)src_cols;
     g.src_col0 = (uint32_t)src_col0;

@@ -176,6 +176,33 @@ extern "C" int gpu_matrix_add_block(GpuMatrix *out, const GpuMatrix *src, size_t
         GP_CHECK_LAUNCH("add_rect_kernel"); return 0;);
 }
 
+// extension: out block += src block * scalar (scalar 1x1, everything EVAL) — one launch instead of mul_scalar + add + the
+// slice/concat copies around them (the vector rows of a stacked BGG encoding product, mxx_b200/bgg.py)
+extern "C" int gpu_matrix_add_scaled_block(GpuMatrix *out, const GpuMatrix *src, const GpuMatrix *scalar, size_t dst_row, size_t dst_col,
+                                           size_t src_row, size_t src_col, size_t rows, size_t cols) {
+    if (binary_check("gpu_matrix_add_scaled_block", out, src, scalar)) return 1;
+    if (scalar->rows != 1 || scalar->cols != 1) return gp::set_error("scalar must be 1x1 in gpu_matrix_add_scaled_block");
+    if (out->format != GPU_POLY_FORMAT_EVAL || src->format != GPU_POLY_FORMAT_EVAL || scalar->format != GPU_POLY_FORMAT_EVAL)
+        return gp::set_error("gpu_matrix_add_scaled_block requires EVAL format");
+    if (src_row + rows > src->rows || src_col + cols > src->cols || dst_row + rows > out->rows || dst_col + cols > out->cols)
+        return gp::set_error("block out of range in gpu_matrix_add_scaled_block");
+    if (rows == 0 || cols == 0 || out->level < 0) return 0;
+    GpuContext *ctx = out->ctx;
+    if (bind_device(ctx)) return 1;
+    const gp::RectGeom g{out->cols, src->cols, dst_row, dst_col, src_row, src_col, rows, cols};
+    return GP_DISPATCH_WIDTH(
+        ctx, const int V = vec_width<T>(ctx); const size_t total = rows * cols * out->poly_words() / V;
+        const unsigned threads = 256, grid = stride_grid(ctx, total, threads);
+        const auto *lc = (const gp::LimbConst<T> *)ctx->d_limb; const uint32_t limbs = (uint32_t)out->limbs(), logn = (uint32_t)ctx->logN;
+        T *d = (T *)out->data; const T *s = (const T *)src->data; const T *z = (const T *)scalar->data;
+        switch (V) {
+            case 4: gp::fma_rect_kernel<T, 4><<<grid, threads, 0, gp::cur(ctx)>>>(d, s, z, g, total, limbs, logn, lc); break;
+            case 2: gp::fma_rect_kernel<T, 2><<<grid, threads, 0, gp::cur(ctx)>>>(d, s, z, g, total, limbs, logn, lc); break;
+            default: gp::fma_rect_kernel<T, 1><<<grid, threads, 0, gp::cur(ctx)>>>(d, s, z, g, total, limbs, logn, lc); break;
+        } gp::count_launch();
+        GP_CHECK_LAUNCH("fma_rect_kernel"); return 0;);
+}
+
 extern "C" int gpu_matrix_mul(GpuMatrix *out, const GpuMatrix *lhs, const GpuMatrix *rhs) {
     if (binary_check("gpu_matrix_mul", out, lhs, rhs)) return 1;
     if (lhs->cols != rhs->rows || out->rows != lhs->rows || out->cols != rhs->cols)

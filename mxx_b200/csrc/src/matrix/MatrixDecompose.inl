@@ -83,19 +83,34 @@ template <typename T> int dispatch_fast_decompose(GpuContext *ctx, const T *src,
     }
 }
 
+// A coefficient-form source that is NOT an ordinary matrix of this context: the all-gathered per-rank blocks of a
+// limb-sharded operand (gp::DecompGeom, ntt.cuh), carrying ALL towers of the full CRT basis
+struct GatheredSrc {
+    uint32_t towers = 0, tpg = 0, crt_bits = 0;
+    size_t group_stride = 0, poly_stride = 0;
+    unsigned char bits[64] = {};
+};
+
 // out (rows*ell x cols) <- digits of src[:, src_col0 : src_col0 + cols] (src in COEFF form)
 template <typename T>
 int run_decompose(GpuContext *ctx, const T *src_coeff, T *out, size_t rows, size_t src_cols, size_t src_col0, size_t cols,
-                  uint32_t limbs, uint32_t base_bits, bool small, bool to_eval) {
-    const uint32_t dpt = digits_per_tower(ctx, base_bits);
-    gp::DecompGeom g;
+                  uint32_t limbs, uint32_t base_bits, bool small, bool to_eval, const GatheredSrc *gs = nullptr) {
+    const uint32_t dpt = gs ? (gs->crt_bits + base_bits - 1) / base_bits : digits_per_tower(ctx, base_bits);
+    gp::DecompGeom g{};
     g.limbs = limbs;
     g.src_cols = (uint32_t)src_cols;
     g.src_col0 = (uint32_t)src_col0;
     g.cols = (uint32_t)cols;
     g.dpt = dpt;
-    g.ell = small ? dpt : dpt * limbs;
+    g.ell = small ? dpt : dpt * (gs ? gs->towers : limbs);
     g.base_bits = base_bits;
+    if (gs) {
+        g.gathered = 1;
+        g.src_tpg = gs->tpg;
+        g.src_group_stride = gs->group_stride;
+        g.src_poly_stride = gs->poly_stride;
+        memcpy(g.tower_bits, gs->bits, sizeof(g.tower_bits));
+    }
     const size_t opl = rows * g.ell * cols * limbs;
     if (opl == 0) return 0;
     if (const int lc = ntt_cluster_log<T>(ctx); to_eval && lc > 0) {  // rings of 2..8 blocks: digits extracted by the cluster's push phase
@@ -236,6 +251,62 @@ extern "C" int gpu_matrix_fill_small_decomposed_identity_chunk(GpuMatrix *out, c
 // column chunk one fused digit+NTT kernel and one product kernel writing straight into the
 // output columns (MXX_MUL_DECOMPOSE_SCRATCH_BYTES bounds the digit scratch; the reference's
 // knob is MXX_MUL_DECOMPOSE_COLUMN_CHUNK_WIDTH, src/env.rs:148).
+namespace {
+// out = lhs * G^-1(source columns [col0, col0 + out->cols)): per column chunk one fused digit+NTT kernel and one product
+// kernel writing straight into the output columns.  `coeff` is the coefficient-form source: an ordinary d x c matrix of
+// this context, or (gs != nullptr) the gathered blocks of a limb-sharded operand.
+template <typename T>
+int mul_decompose_core(GpuContext *ctx, GpuMatrix *out, const GpuMatrix *lhs, const T *coeff, size_t d, size_t c, size_t col0,
+                       size_t m, uint32_t base_bits, bool small, const GatheredSrc *gs) {
+    // digit polynomials in flight: two lanes of at most this many bytes each (they stream through L2/HBM while
+    // the issue-bound digit-NTT kernel runs, so the traffic is hidden; the cap only bounds scratch memory)
+    size_t budget = 2ull << 30;
+    if (const char *env = getenv("MXX_MUL_DECOMPOSE_SCRATCH_BYTES")) {
+        char *end = nullptr;
+        unsigned long long v = strtoull(env, &end, 10);
+        if (end && end != env && v) budget = v;
+    }
+    const uint32_t limbs = (uint32_t)out->limbs();
+    const size_t oc = out->cols;
+    // Column chunks are independent (SURVEY 8e).  Chunk k runs on auxiliary stream k % 2 with its own
+    // digit buffer, so the partial last wave of one chunk's digit-NTT kernel is filled by the next
+    // chunk's CTAs and the HBM/L2-bound product kernel overlaps the issue-bound NTT kernel.
+    const size_t poly_bytes = out->poly_words() * sizeof(T);
+    // Wide chunks: a digit-NTT launch of w columns has w*m*limbs CTAs, and only a launch of many waves keeps
+    // the last, partial wave cheap (C3-a: 450 CTAs per column on 444 resident slots).  Two chunks run
+    // concurrently on the two auxiliary streams, so one chunk's product overlaps the other's NTTs.
+    size_t width = std::max<size_t>(1, (budget / 2) / std::max<size_t>(1, m * poly_bytes));
+    width = std::min(width, oc >= 2 ? (oc + 1) / 2 : oc);
+    const size_t chunks = (oc + width - 1) / width;
+    const int lanes = chunks > 1 ? 2 : 1;
+    Scratch digits[2];
+    for (int i = 0; i < lanes; i++)
+        if (digits[i].alloc(m * width * poly_bytes, ctx->stream)) return 1;
+    if (lanes > 1) {
+        GP_CUDA(cudaEventRecord(ctx->ev_fork, ctx->stream), "cudaEventRecord(fork)");
+        for (int i = 0; i < lanes; i++) GP_CUDA(cudaStreamWaitEvent(ctx->aux[i], ctx->ev_fork, 0), "cudaStreamWaitEvent(fork)");
+    }
+    int st = 0;
+    for (size_t k = 0; k < chunks && !st; k++) {
+        const size_t c0 = k * width, w = std::min(width, oc - c0);
+        gp::StreamScope scope(lanes > 1 ? ctx->aux[k & 1] : ctx->stream);
+        T *dg = (T *)digits[lanes > 1 ? (k & 1) : 0].p;
+        st = run_decompose<T>(ctx, coeff, dg, d, c, col0 + c0, w, limbs, base_bits, small, true, gs);
+        if (st) break;
+        gp::MatmulGeom g{};
+        g.rows = (uint32_t)lhs->rows; g.inner = (uint32_t)m; g.cols = (uint32_t)w; g.b_cols = (uint32_t)w; g.b_col0 = 0;
+        g.out_cols = (uint32_t)oc; g.out_col0 = (uint32_t)c0; g.limbs = limbs;
+        st = run_matmul<T>(ctx, (T *)out->data, (const T *)lhs->data, dg, g);
+    }
+    if (lanes > 1)  // join even after an error so the scratch buffers are not freed under running kernels
+        for (int i = 0; i < lanes; i++) {
+            cudaEventRecord(ctx->ev_join[i], ctx->aux[i]);
+            cudaStreamWaitEvent(ctx->stream, ctx->ev_join[i], 0);
+        }
+    return st;
+}
+}  // namespace
+
 extern "C" int gpu_matrix_mul_decompose(GpuMatrix *out, const GpuMatrix *lhs, const GpuMatrix *rhs, uint32_t base_bits, int small) {
     if (binary_check("gpu_matrix_mul_decompose", out, lhs, rhs)) return 1;
     if (base_bits == 0 || base_bits >= 63) return gp::set_error("invalid base_bits in gpu_matrix_mul_decompose");
@@ -252,53 +323,51 @@ extern "C" int gpu_matrix_mul_decompose(GpuMatrix *out, const GpuMatrix *lhs, co
     out->format = GPU_POLY_FORMAT_EVAL;
     if (out->polys() == 0) return 0;
     if (bind_device(ctx)) return 1;
-    // digit polynomials in flight: two lanes of at most this many bytes each (they stream through L2/HBM while
-    // the issue-bound digit-NTT kernel runs, so the traffic is hidden; the cap only bounds scratch memory)
-    size_t budget = 2ull << 30;
-    if (const char *env = getenv("MXX_MUL_DECOMPOSE_SCRATCH_BYTES")) {
-        char *end = nullptr;
-        unsigned long long v = strtoull(env, &end, 10);
-        if (end && end != env && v) budget = v;
-    }
     const uint32_t limbs = (uint32_t)out->limbs();
-    // Column chunks are independent (SURVEY 8e).  Chunk k runs on auxiliary stream k % 2 with its own
-    // digit buffer, so the partial last wave of one chunk's digit-NTT kernel is filled by the next
-    // chunk's CTAs and the HBM/L2-bound product kernel overlaps the issue-bound NTT kernel.
     return GP_DISPATCH_WIDTH(
-        ctx, const size_t poly_bytes = out->poly_words() * sizeof(T);
-        // Wide chunks: a digit-NTT launch of w columns has w*m*limbs CTAs, and only a launch of many waves keeps
-        // the last, partial wave cheap (C3-a: 450 CTAs per column on 444 resident slots).  Two chunks run
-        // concurrently on the two auxiliary streams, so one chunk's product overlaps the other's NTTs.
-        size_t width = std::max<size_t>(1, (budget / 2) / std::max<size_t>(1, m * poly_bytes));
-        width = std::min(width, c >= 2 ? (c + 1) / 2 : c);
-        const size_t chunks = (c + width - 1) / width; const int lanes = chunks > 1 ? 2 : 1;
-        const T *coeff = (const T *)rhs->data; Scratch tmp; Scratch digits[2];
+        ctx, const T *coeff = (const T *)rhs->data; Scratch tmp;
         if (rhs->format == GPU_POLY_FORMAT_EVAL) {
             if (tmp.alloc(rhs->bytes(), ctx->stream)) return 1;
             if (run_ntt_inv<T>(ctx, (const T *)rhs->data, (T *)tmp.p, rhs->polys(), limbs)) return 1;
             coeff = (const T *)tmp.p;
-        }
-        for (int i = 0; i < lanes; i++) if (digits[i].alloc(m * width * poly_bytes, ctx->stream)) return 1;
-        if (lanes > 1) {
-            GP_CUDA(cudaEventRecord(ctx->ev_fork, ctx->stream), "cudaEventRecord(fork)");
-            for (int i = 0; i < lanes; i++) GP_CUDA(cudaStreamWaitEvent(ctx->aux[i], ctx->ev_fork, 0), "cudaStreamWaitEvent(fork)");
-        }
-        int st = 0;
-        for (size_t k = 0; k < chunks && !st; k++) {
-            const size_t c0 = k * width, w = std::min(width, c - c0);
-            gp::StreamScope scope(lanes > 1 ? ctx->aux[k & 1] : ctx->stream);
-            T *dg = (T *)digits[lanes > 1 ? (k & 1) : 0].p;
-            st = run_decompose<T>(ctx, coeff, dg, d, c, c0, w, limbs, base_bits, small != 0, true);
-            if (st) break;
-            gp::MatmulGeom g{};
-            g.rows = (uint32_t)lhs->rows; g.inner = (uint32_t)m; g.cols = (uint32_t)w; g.b_cols = (uint32_t)w; g.b_col0 = 0;
-            g.out_cols = (uint32_t)c; g.out_col0 = (uint32_t)c0; g.limbs = limbs;
-            st = run_matmul<T>(ctx, (T *)out->data, (const T *)lhs->data, dg, g);
-        }
-        if (lanes > 1)  // join even after an error so the scratch buffers are not freed under running kernels
-            for (int i = 0; i < lanes; i++) {
-                cudaEventRecord(ctx->ev_join[i], ctx->aux[i]);
-                cudaStreamWaitEvent(ctx->stream, ctx->ev_join[i], 0);
-            }
-        return st;);
+        } return mul_decompose_core<T>(ctx, out, lhs, coeff, d, c, 0, m, base_bits, small != 0, nullptr););
+}
+
+// ---- extension: the same for a LIMB-SHARDED job (SURVEY 8e "Alternative (limbs)", mxx_b200/dist.py) -----------------
+// `out` and `lhs` live in this rank's context, whose moduli are a subset of the job's CRT basis; `other_coeff` is the
+// coefficient-form right operand (d x c polynomials) with ALL `towers` towers of the basis, as the all-gather of the ranks'
+// [poly][towers_per_group][n] blocks left it: tower t of polynomial p at
+//     (t / towers_per_group) * group_stride_words + p * poly_stride_words + (t % towers_per_group) * n   words
+// (an ordinary full-basis matrix is towers_per_group = towers, poly_stride_words = towers * n).  Words have the width of
+// this context's storage.  out (lhs->rows x cols) = lhs * G^-1(other[:, col0 : col0 + cols]) restricted to this rank's
+// limbs; digit rows follow the FULL basis (ell = digits_per_tower(max tower bits) * towers, or digits_per_tower if small).
+extern "C" int gpu_matrix_mul_decompose_gathered(GpuMatrix *out, const GpuMatrix *lhs, const void *other_coeff, size_t d, size_t c,
+                                                 size_t col0, const uint64_t *tower_moduli, size_t towers, size_t towers_per_group,
+                                                 size_t group_stride_words, size_t poly_stride_words, uint32_t base_bits, int small) {
+    const char *fn = "gpu_matrix_mul_decompose_gathered";
+    if (!out || !lhs || !tower_moduli || (!other_coeff && d * c)) return gp::set_error(std::string("invalid ") + fn + " arguments");
+    if (!same_ctx(out, lhs)) return gp::set_error(std::string("context mismatch in ") + fn);
+    if (base_bits == 0 || base_bits >= 63) return gp::set_error(std::string("invalid base_bits in ") + fn);
+    if (out->level < 0) return gp::set_error(std::string("invalid level in ") + fn);
+    if (towers == 0 || towers > 64 || towers_per_group == 0 || towers % towers_per_group)
+        return gp::set_error(std::string("invalid tower grouping in ") + fn);
+    GpuContext *ctx = out->ctx;
+    GatheredSrc gs;
+    gs.towers = (uint32_t)towers, gs.tpg = (uint32_t)towers_per_group;
+    gs.group_stride = group_stride_words, gs.poly_stride = poly_stride_words;
+    for (size_t t = 0; t < towers; t++) {
+        if (tower_moduli[t] < 2) return gp::set_error(std::string("invalid tower modulus in ") + fn);
+        gs.bits[t] = (unsigned char)(64 - __builtin_clzll(tower_moduli[t]));
+        gs.crt_bits = std::max<uint32_t>(gs.crt_bits, gs.bits[t]);
+        if (!ctx->wide && gs.bits[t] > 30) return gp::set_error(std::string("tower does not fit this context's 32-bit words in ") + fn);
+    }
+    const size_t dpt = (gs.crt_bits + base_bits - 1) / base_bits;
+    const size_t ell = small ? dpt : dpt * towers, m = d * ell;
+    if (lhs->cols != m || out->rows != lhs->rows || col0 + out->cols > c) return gp::set_error(std::string("size mismatch in ") + fn);
+    if (lhs->format != GPU_POLY_FORMAT_EVAL) return gp::set_error(std::string(fn) + " requires an EVAL left operand");
+    if (out == lhs || (out->data && out->data == lhs->data)) return gp::set_error(std::string(fn) + " output must not alias an input");
+    out->format = GPU_POLY_FORMAT_EVAL;
+    if (out->polys() == 0) return 0;
+    if (bind_device(ctx)) return 1;
+    return GP_DISPATCH_WIDTH(ctx, return mul_decompose_core<T>(ctx, out, lhs, (const T *)other_coeff, d, c, col0, m, base_bits, small != 0, &gs););
 }

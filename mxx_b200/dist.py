@@ -1,4 +1,7 @@
-"""Column-block sharding of the DCRT matrix path over one process per GPU.
+"""Sharding of the DCRT matrix path over one process per GPU: output-column blocks, RNS limbs, or a 2-D grid of both.
+
+Columns (`ColumnShardedOps`) are the primary axis; `GridShardedOps` (below) adds the limb axis of SURVEY.md 8e
+"Alternative (limbs)" and the 2-D (limb group x column block) partition the north star names.
 
 The path shards along OUTPUT COLUMNS: column j of A*B or of S*G^-1(other) depends only
 on column j of the right operand and on all of the left operand — this is literally how the reference
@@ -98,6 +101,39 @@ def device_tensor(mat: GpuDCRTPolyMatrix):
     return torch.as_tensor(_DeviceBytes(ptr.value, nbytes), device=f"cuda:{mat.params.gpu_ids[0]}")
 
 
+def all_gather_columns_into(out: GpuDCRTPolyMatrix, local: GpuDCRTPolyMatrix, sh: ColumnShards, rank: int, group=None) -> None:
+    """out[:, block r] <- rank r's `local`, for every rank of `group`, straight into `out`'s storage.
+
+    Storage is [row][col][limb][n], so the column blocks of ONE row are contiguous and in rank order: with equal block
+    widths a row is exactly the receive buffer of an all-gather whose send buffer is the local row — one
+    `all_gather_into_tensor` (ncclAllGather) per row, no staging matrices, no placement kernels.  Ragged widths go
+    through a padded all-gather and gpu_matrix_copy_block.  Call under the context's stream (ColumnShardedOps._stream)."""
+    torch, dist = _torch()
+    world = sh.world
+    if world == 1:
+        out.copy_block_from(local, 0, 0, 0, 0, local.nrow, local.ncol)
+        return
+    p = local.params
+    if len(set(sh.counts)) == 1:
+        dst, src = device_tensor(out), device_tensor(local)
+        row_out, row_loc = dst.numel() // max(out.nrow, 1), src.numel() // max(local.nrow, 1)
+        for r in range(local.nrow):
+            dist.all_gather_into_tensor(dst[r * row_out:(r + 1) * row_out], src[r * row_loc:(r + 1) * row_loc], group=group)
+        out.is_ntt = local.is_ntt
+        return
+    width = sh.max_count
+    send = local
+    if local.ncol != width:  # pad: copy into a wider block
+        send = GpuDCRTPolyMatrix(p, local.nrow, width, level=local.level, is_ntt=local.is_ntt)
+        send.copy_block_from(local, 0, 0, 0, 0, local.nrow, local.ncol)
+    recv = GpuDCRTPolyMatrix(p, world * local.nrow, width, level=local.level, is_ntt=local.is_ntt)
+    dist.all_gather_into_tensor(device_tensor(recv), device_tensor(send), group=group)
+    for r in range(world):
+        c0, c1 = sh.range(r)
+        if c1 > c0:
+            out.copy_block_from(recv, 0, c0, r * local.nrow, 0, local.nrow, c1 - c0)
+
+
 class ColumnShardedOps:
     """The hot path on this rank's column block + the NCCL assembly step."""
 
@@ -131,28 +167,14 @@ class ColumnShardedOps:
 
     # -- assembly: one all-gather over NVLink ---------------------------------------------------
     def all_gather_columns(self, local: GpuDCRTPolyMatrix, ncol: int) -> GpuDCRTPolyMatrix:
-        """(nrow x ncol) matrix on every rank from the ranks' column blocks; device buffers go to NCCL
-        directly.  Blocks travel padded to the widest block (gpu_matrix_copy_block places them)."""
-        torch, dist = _torch()
+        """(nrow x ncol) matrix on every rank from the ranks' column blocks; device buffers go to NCCL directly."""
         sh = self.shards(ncol)
         assert local.ncol == sh.counts[self.rank], "local block does not match the sharding"
         if self.world == 1:
             return local.clone()
-        p = self.params
-        width = sh.max_count
-        send = local
-        if local.ncol != width:  # pad: copy into a zero-extended block
-            send = GpuDCRTPolyMatrix(p, local.nrow, width, level=local.level, is_ntt=local.is_ntt)
-            send.copy_block_from(local, 0, 0, 0, 0, local.nrow, local.ncol)
-        recv = [GpuDCRTPolyMatrix(p, local.nrow, width, level=local.level, is_ntt=local.is_ntt) for _ in range(self.world)]
-        tensors = [device_tensor(m) for m in recv]
-        with self._stream():  # ordered after the kernels that produced `send`, before the copies below
-            dist.all_gather(tensors, device_tensor(send), group=self.group)
-        out = GpuDCRTPolyMatrix(p, local.nrow, ncol, level=local.level, is_ntt=local.is_ntt)
-        for r, m in enumerate(recv):
-            c0, c1 = sh.range(r)
-            if c1 > c0:
-                out.copy_block_from(m, 0, c0, 0, 0, local.nrow, c1 - c0)
+        out = GpuDCRTPolyMatrix(self.params, local.nrow, ncol, level=local.level, is_ntt=local.is_ntt)
+        with self._stream():  # ordered after the kernels that produced `local`
+            all_gather_columns_into(out, local, sh, self.rank, self.group)
         return out
 
     def broadcast(self, mat: GpuDCRTPolyMatrix, src: int = 0) -> None:
@@ -162,3 +184,143 @@ class ColumnShardedOps:
             return
         with self._stream():
             dist.broadcast(device_tensor(mat), src=src, group=self.group)
+
+
+# ---- 2-D partition: limb groups x column blocks --------------------------------------------------------------------
+class GridShards:
+    """rank = a * col_groups + b owns limb group a (towers [a*tpg, (a+1)*tpg) of the CRT basis) and column block b.
+
+    SURVEY.md 8e: NTT, INTT and the MAC are limb-local; only digit extraction reads source tower t to write every limb.
+    So a limb group needs the COEFFICIENT form of the right operand at all towers — one all-gather along the limb axis
+    of the small operand — and nothing else; the column axis needs nothing during compute and one all-gather to hand a
+    result on as the next left operand."""
+
+    def __init__(self, towers: int, limb_groups: int, col_groups: int):
+        if limb_groups < 1 or col_groups < 1 or towers % limb_groups:
+            raise ValueError("the limb groups must divide the CRT depth")
+        self.towers, self.limb_groups, self.col_groups = int(towers), int(limb_groups), int(col_groups)
+        self.tpg = self.towers // self.limb_groups
+        self.world = self.limb_groups * self.col_groups
+
+    def coords(self, rank: int) -> tuple[int, int]:
+        return divmod(rank, self.col_groups)
+
+    def tower_range(self, a: int) -> tuple[int, int]:
+        return a * self.tpg, (a + 1) * self.tpg
+
+    def limb_axis_ranks(self, b: int) -> list[int]:
+        return [a * self.col_groups + b for a in range(self.limb_groups)]
+
+    def col_axis_ranks(self, a: int) -> list[int]:
+        return [a * self.col_groups + b for b in range(self.col_groups)]
+
+    def slice_host(self, full: np.ndarray, rank: int, ncol_sharded: bool = True) -> np.ndarray:
+        """this rank's towers (and, if ncol_sharded, columns) of a host matrix (nrow, ncol, towers, n)"""
+        a, b = self.coords(rank)
+        t0, t1 = self.tower_range(a)
+        if ncol_sharded:
+            c0, c1 = ColumnShards(full.shape[1], self.col_groups).range(b)
+            return np.ascontiguousarray(full[:, c0:c1, t0:t1])
+        return np.ascontiguousarray(full[:, :, t0:t1])
+
+
+def towers_from_gathered_host(gathered: np.ndarray, d: int) -> np.ndarray:
+    """(groups*d, c, tpg, n) gathered layout -> (d, c, groups*tpg, n) ordinary layout (host; tests and checks)"""
+    groups = gathered.shape[0] // d
+    g = gathered.reshape(groups, d, gathered.shape[1], gathered.shape[2], gathered.shape[3])
+    return np.ascontiguousarray(g.transpose(1, 2, 0, 3, 4).reshape(d, gathered.shape[1], groups * gathered.shape[2], gathered.shape[3]))
+
+
+def all_gather_towers_host(local_coeff: np.ndarray, group=None) -> np.ndarray:
+    """host twin of GridShardedOps.gather_towers: (d, c, tpg, n) per rank -> (groups*d, c, tpg, n), rank-major"""
+    torch, dist = _torch()
+    mine = torch.from_numpy(np.ascontiguousarray(local_coeff).view(np.int64))
+    world = dist.get_world_size(group)
+    out = torch.empty((world * mine.shape[0],) + tuple(mine.shape[1:]), dtype=mine.dtype)
+    dist.all_gather_into_tensor(out, mine, group=group)
+    return out.numpy().view(np.uint64)
+
+
+class GridShardedOps:
+    """The hot path on this rank's (limb group, column block) + the two assembly collectives.
+
+    `moduli` is the job's full CRT basis; this rank's context holds only its limb group's moduli (NTT tables, storage
+    and every kernel see `tpg` limbs).  Digit geometry (digits per tower, row order) follows the FULL basis."""
+
+    def __init__(self, ring_dimension: int, moduli, base_bits: int, limb_groups: int, col_groups: int, device: int = 0, group=None):
+        torch, dist = _torch()
+        from .params import GpuDCRTPolyParams
+
+        self.full_moduli = [int(q) for q in moduli]
+        self.grid = GridShards(len(self.full_moduli), limb_groups, col_groups)
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        if self.world != self.grid.world:
+            raise ValueError("limb_groups * col_groups must equal the number of ranks")
+        self.a, self.b = self.grid.coords(self.rank)
+        t0, t1 = self.grid.tower_range(self.a)
+        self.params = GpuDCRTPolyParams(ring_dimension, self.full_moduli[t0:t1], base_bits, gpu_ids=(device,))
+        self.base_bits = int(base_bits)
+        self.crt_bits = max(q.bit_length() for q in self.full_moduli)
+        self.dpt = -(-self.crt_bits // self.base_bits)
+        self.ell = self.dpt * len(self.full_moduli)
+        # sub-communicators: every rank creates every group, in the same order (torch.distributed.new_group is collective)
+        self.limb_group, self.col_group = group, group
+        if self.world > 1 and col_groups > 1 and limb_groups > 1:
+            for b in range(col_groups):
+                g = dist.new_group(self.grid.limb_axis_ranks(b))
+                if b == self.b:
+                    self.limb_group = g
+            for a in range(limb_groups):
+                g = dist.new_group(self.grid.col_axis_ranks(a))
+                if a == self.a:
+                    self.col_group = g
+        self._ext = None
+
+    def _stream(self):
+        torch, _ = _torch()
+        if self._ext is None:
+            self._ext = torch.cuda.ExternalStream(self.params.stream(), device=f"cuda:{self.params.gpu_ids[0]}")
+        return torch.cuda.stream(self._ext)
+
+    def col_shards(self, ncol: int) -> ColumnShards:
+        return ColumnShards(ncol, self.grid.col_groups)
+
+    # -- the limb-axis exchange: coefficient form of the right operand, all towers ---------------------------------
+    def gather_towers(self, other_local: GpuDCRTPolyMatrix) -> GpuDCRTPolyMatrix:
+        """(d x c) on this rank's towers, EVAL or COEFF -> (limb_groups*d x c) COEFF matrix of this rank's context whose
+        rows [g*d, (g+1)*d) hold limb group g's towers (the layout gpu_matrix_mul_decompose_gathered reads)."""
+        torch, dist = _torch()
+        coeff = other_local
+        if other_local.is_ntt:
+            coeff = other_local.clone()
+            coeff.intt_all_in_place()
+        if self.grid.limb_groups == 1:
+            return coeff if coeff is not other_local else other_local.clone()
+        out = GpuDCRTPolyMatrix(self.params, self.grid.limb_groups * coeff.nrow, coeff.ncol, level=coeff.level, is_ntt=False)
+        with self._stream():
+            dist.all_gather_into_tensor(device_tensor(out), device_tensor(coeff), group=self.limb_group)
+        return out
+
+    # -- compute ------------------------------------------------------------------------------------------------------
+    def mul(self, lhs_local_limbs: GpuDCRTPolyMatrix, rhs_local: GpuDCRTPolyMatrix) -> GpuDCRTPolyMatrix:
+        """this rank's (limbs, columns) of lhs * rhs: limb-local, no exchange"""
+        return lhs_local_limbs * rhs_local
+
+    def mul_decompose(self, lhs_local_limbs: GpuDCRTPolyMatrix, other_local: GpuDCRTPolyMatrix, small: bool = False) -> GpuDCRTPolyMatrix:
+        """this rank's (limbs, columns) of lhs * G^-1(other): one all-gather of the coefficient-form `other` block along
+        the limb axis, then digits + NTT + MAC on the local limbs (lhs: all columns of S on this rank's limbs)"""
+        gathered = self.gather_towers(other_local)
+        return lhs_local_limbs.mul_decompose_gathered(gathered, other_local.nrow, self.full_moduli, self.grid.tpg, small=small)
+
+    # -- the column-axis exchange ---------------------------------------------------------------------------------------
+    def all_gather_columns(self, local: GpuDCRTPolyMatrix, ncol: int) -> GpuDCRTPolyMatrix:
+        """(nrow x ncol) on this rank's limbs from the column blocks of the ranks that share its limb group"""
+        sh = self.col_shards(ncol)
+        assert local.ncol == sh.counts[self.b], "local block does not match the sharding"
+        if self.grid.col_groups == 1:
+            return local
+        out = GpuDCRTPolyMatrix(self.params, local.nrow, ncol, level=local.level, is_ntt=local.is_ntt)
+        with self._stream():
+            all_gather_columns_into(out, local, sh, self.b, self.col_group)
+        return out

@@ -540,6 +540,37 @@ class GpuDCRTPolyMatrix:
             out.copy_block_from(prod, 0, c0, 0, 0, self.nrow, c1 - c0)
         return out
 
+    def mul_decompose_gathered(self, gathered, d: int, tower_moduli, towers_per_group: int, small: bool = False,
+                               col0: int = 0, ncol: int | None = None):
+        """S * G^-1(other) for a LIMB-SHARDED job (extension gpu_matrix_mul_decompose_gathered; mxx_b200/dist.py).
+
+        self lives in this rank's context (its subset of the CRT basis).  `gathered` is the coefficient-form right
+        operand with ALL towers, as the all-gather of the ranks' (d x c) blocks leaves it: a (groups*d) x c COEFF matrix
+        of this context whose rows [g*d, (g+1)*d) are limb group g's towers.  Digit rows follow the full basis
+        `tower_moduli`.  Returns the product on this rank's limbs, columns [col0, col0 + ncol) of `other`."""
+        import ctypes as C
+
+        towers = len(tower_moduli)
+        assert towers % towers_per_group == 0 and gathered.nrow == (towers // towers_per_group) * d and not gathered.is_ntt
+        assert gathered.level + 1 == towers_per_group == self.level + 1
+        c = gathered.ncol
+        ncol = c - col0 if ncol is None else ncol
+        n = self.params.ring_dimension
+        ptr, wb, fmt = C.c_void_p(), C.c_int(), C.c_int()
+        check_status(self._L.gpu_matrix_device_info(gathered.raw, C.byref(ptr), C.byref(wb), C.byref(fmt)), "gpu_matrix_device_info", self._L)
+        out = GpuDCRTPolyMatrix(self.params, self.nrow, ncol, self.level, True)
+        mod = (C.c_uint64 * towers)(*[int(q) for q in tower_moduli])
+        poly_stride = towers_per_group * n
+        check_status(self._L.gpu_matrix_mul_decompose_gathered(out.raw, self._eval().raw, ptr, d, c, col0, mod, towers, towers_per_group,
+                                                               d * c * poly_stride, poly_stride, self.params.base_bits, int(small)),
+                     "gpu_matrix_mul_decompose_gathered", self._L)
+        return out
+
+    def add_scaled_block_from(self, src, scalar, dst_row, dst_col, src_row, src_col, rows, cols):
+        """self[block] += src[block] * scalar (scalar 1x1; all EVAL) in one launch (extension gpu_matrix_add_scaled_block)"""
+        check_status(self._L.gpu_matrix_add_scaled_block(self.raw, src.raw, scalar.raw, dst_row, dst_col, src_row, src_col, rows, cols),
+                     "gpu_matrix_add_scaled_block", self._L)
+
     def mul_decompose_small(self, other, fused: bool | None = None):
         return self.mul_decompose(other, fused=fused, small=True)
 

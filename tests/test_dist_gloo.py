@@ -102,3 +102,73 @@ def test_all_gather_columns_nccl_two_gpus():
                         "--master-port", str(_free_port()), os.path.join(ROOT, "tests", "nccl_assembly_check.py")],
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+# ---- limb groups / 2-D grid (SURVEY.md 8e "Alternative (limbs)") ---------------------------------------------------------
+def test_grid_shards_cover_every_unit_once():
+    from mxx_b200.dist import GridShards
+
+    for towers, lg, cg, ncol in ((8, 1, 8, 24), (8, 8, 1, 24), (8, 2, 4, 24), (16, 4, 2, 32), (15, 3, 1, 30), (4, 2, 2, 5)):
+        g = GridShards(towers, lg, cg)
+        seen = set()
+        for rank in range(g.world):
+            a, b = g.coords(rank)
+            assert rank in g.limb_axis_ranks(b) and rank in g.col_axis_ranks(a)
+            t0, t1 = g.tower_range(a)
+            c0, c1 = ColumnShards(ncol, cg).range(b)
+            for t in range(t0, t1):
+                for c in range(c0, c1):
+                    assert (t, c) not in seen
+                    seen.add((t, c))
+        assert len(seen) == towers * ncol  # every (limb, column) unit has exactly one owner
+    with pytest.raises(ValueError):
+        GridShards(15, 2, 1)  # the limb groups must divide the CRT depth
+
+
+def _limb_worker(rank, world, port, q):
+    try:
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+        import torch.distributed as dist
+
+        from mxx_b200.dist import GridShards, all_gather_towers_host, towers_from_gathered_host
+        from oracle import oracle as orc
+
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+        n, bits, depth, bb, d, ncol = 64, 24, 4, 12, 2, 3
+        moduli = orc.prime_chain(n, bits, depth)
+        plan = orc.Plan(n, moduli)
+        grid = GridShards(depth, world, 1)
+        t0, t1 = grid.tower_range(rank)
+        sub = orc.Plan(n, moduli[t0:t1])
+        ell = plan.ell(bb)
+        S, other = plan.uniform(2, d * ell, seed=11), plan.uniform(d, ncol, seed=12)
+        # this rank holds its towers only: INTT is limb-local, then ONE all-gather of the coefficient form
+        local_coeff = sub.intt(grid.slice_host(other, rank, ncol_sharded=False))
+        gathered = all_gather_towers_host(local_coeff)
+        coeff_full = towers_from_gathered_host(gathered, d)
+        ok = np.array_equal(coeff_full, plan.intt(other))
+        # digits follow the FULL basis; NTT and the MAC run on the local towers only
+        digits = plan.decompose(coeff_full, bb)[:, :, t0:t1]
+        out_local = sub.mul(grid.slice_host(S, rank, ncol_sharded=False), sub.ntt(np.ascontiguousarray(digits)))
+        ok = ok and np.array_equal(out_local, plan.mul_decompose(S, other, bb)[:, :, t0:t1])
+        dist.barrier()
+        dist.destroy_process_group()
+        q.put((rank, bool(ok), ""))
+    except Exception as e:  # pragma: no cover
+        q.put((rank, False, repr(e)))
+
+
+def test_limb_sharded_result_equals_unsharded_gloo_world2():
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_limb_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, ok, err in res:
+        assert ok, f"rank {rank}: limb-sharded != unsharded {err}"
