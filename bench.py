@@ -37,12 +37,14 @@ sys.path.insert(0, ROOT)
 
 # ---- workload definitions ---------------------------------------------
 C1R = dict(name="C1-R", n=1 << 14, depth=15, bits=24, bb=12, r=1, k=30, c=120)
-C3A = dict(name="C3-a", n=1 << 14, depth=15, bits=24, bb=12, r=1, d=1, c=30)
-NTT_CASES = [  # (n, depth, bits): ~256 MiB of device residues per batch (> the 126 MB L2)
-    (1 << 14, 16, 28), (1 << 15, 8, 28), (1 << 16, 8, 28),
-    (1 << 14, 8, 51), (1 << 15, 8, 51), (1 << 16, 4, 51),
-]
-NTT_BATCH_BYTES = 256 << 20
+C1J = [dict(name="C1-J 8x8", n=1 << 12, depth=4, bits=50, bb=17, r=8, k=8, c=8), dict(name="C1-J 16x16", n=1 << 12, depth=4, bits=50, bb=17, r=16, k=16, c=16)]
+C3 = [dict(name="C3-a", n=1 << 14, depth=15, bits=24, bb=12, r=1, d=1, c=30, oracle_cols=30),
+      dict(name="C3-b", n=1 << 14, depth=15, bits=24, bb=12, r=4, d=4, c=120, oracle_cols=1),
+      dict(name="C3-c", n=1 << 14, depth=4, bits=51, bb=17, r=2, d=2, c=24, oracle_cols=24)]
+C4 = [dict(name="C4 L=8x51-bit", n=1 << 15, depth=8, bits=51, bb=17, d=1), dict(name="C4 L=16x28-bit", n=1 << 15, depth=16, bits=28, bb=14, d=1)]
+# C2: n in {2^14, 2^15, 2^16} x L in {4, 8, 16} x {28-bit, 51-bit}, 1 GiB of device residues per batch
+NTT_CASES = [(1 << ln, depth, bits) for bits in (28, 51) for ln in (14, 15, 16) for depth in (4, 8, 16)]
+NTT_BATCH_BYTES = 1 << 30
 NCU_MATMUL_TRAFFIC = 3572995000 + 98338048  # bytes per C1-R launch, measured once with ncu (profiles/r01_ncu_v5_summary.txt)
 
 
@@ -52,6 +54,24 @@ def peaks():
         with open(path) as f:
             return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def c1r_config():
+    """the `config` object of BOTH arms (ours and --impl reference): identical by construction"""
+    cfg = C1R
+    return {"workload": "C1-R bench_matrix_mul: DCRTPolyMatrix 1x30 * 30x120, n=2^14, 15 CRT limbs x 24 bit, EVAL operands "
+                        "(benches/bench_matrix_mul_cpu.rs:10-16)", "ring_dim": cfg["n"], "limbs": cfg["depth"], "crt_bits": cfg["bits"],
+            "shape": [cfg["r"], cfg["k"], cfg["c"]],
+            "per_gpu": "column block: A 1x30 replicated, each rank owns 120 columns of B and of the result (job = 1x30 * 30x(120*N)); value counts 120-column products",
+            "l2": "inputs (3.57 GB) exceed the 126 MB L2"}
+
+
+def host_threads() -> int:
+    """threads the CPU legs use: every core this process may run on, whatever OMP_NUM_THREADS says (torchrun exports 1)"""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
 
 
 def uniform_host(out: np.ndarray, moduli, seed: int, threads: int = 8) -> None:
@@ -189,36 +209,50 @@ def make_params(cfg, device):
     return GpuDCRTPolyParams(cfg["n"], moduli, cfg.get("bb", 12), gpu_ids=(device,)), moduli
 
 
+def ntt_traffic_table():
+    """ncu dram__bytes_read.sum + dram__bytes_write.sum per (n, limbs, bits) round trip (tools/ntt_traffic.py -> profiles/)"""
+    path = os.path.join(ROOT, "profiles", "r02_ntt_traffic.json")
+    if not os.path.exists(path):
+        return {}
+    with open(path) as f:
+        return {tuple(r["key"]): r for r in json.load(f)["rows"]}
+
+
 def bench_ntt(device, steps, warmup, hbm_peak, ip=None):
-    """configs[1]: batched NTT -> INTT round trips; Gcoeff/s per direction against the HBM roofline."""
+    """configs[1] (C2): batched INTT -> NTT round trips over 1 GiB of device residues; Gcoeff/s per direction against the
+    HBM roofline and the measured butterfly-issue roofline.  The batch is drawn on the device (uniform sampler); the
+    round trip must return it bit for bit (gpu_matrix_equal against a copy) — comparison with the oracle at these ring
+    sizes is tests/test_round2_gpu.py."""
     from mxx_b200 import GpuDCRTPolyMatrix, ffi
 
     out = []
+    traffic = ntt_traffic_table()
+    L = ffi.lib()
     for n, depth, bits in NTT_CASES:
         cfg = dict(n=n, depth=depth, bits=bits, bb=14)
         params, moduli = make_params(cfg, device)
         W = 4 if max(moduli) < (1 << 30) else 8
         P = max(1, NTT_BATCH_BYTES // (W * depth * n))
-        host = np.empty((1, P, depth, n), dtype=np.uint64)
-        uniform_host(host, moduli, seed=0x6D7878_0002)
-        m = GpuDCRTPolyMatrix.from_rns(params, host, is_ntt=False)
-        L = ffi.lib()
+        m = GpuDCRTPolyMatrix.sample_distribution(params, 1, P, 0, 0.0, [n, depth, bits, 0x6D7878])
+        ref = m.clone()
 
         def step():
-            ffi.check_status(L.gpu_matrix_ntt_all(m.raw), "gpu_matrix_ntt_all")
-            m.is_ntt = True
             ffi.check_status(L.gpu_matrix_intt_all(m.raw), "gpu_matrix_intt_all")
             m.is_ntt = False
+            ffi.check_status(L.gpu_matrix_ntt_all(m.raw), "gpu_matrix_ntt_all")
+            m.is_ntt = True
 
         for _ in range(warmup):
             step()
         params.synchronize()
+        launches0 = L.gpu_kernel_launch_count()
         t = params.timer()
         t.start()
         for _ in range(steps):
             step()
         t.stop()
         ms = t.elapsed_ms() / steps
+        launches = (L.gpu_kernel_launch_count() - launches0) // steps
         coeffs = P * depth * n
         algo_bytes = 2 * (2 * W * coeffs)  # one read + one write per coefficient, two directions
         gbs = algo_bytes / (ms * 1e-3) / 1e9
@@ -232,26 +266,29 @@ def bench_ntt(device, steps, warmup, hbm_peak, ip=None):
             peak = 2.0 / (1.0 / ip[kf] + 1.0 / ip[ki])
             int_roof = {"bound": "fp64-issue" if kf == "bfly_fwd_f64" else "int-issue", "achieved": round(bfly_s, 0), "peak": round(peak, 0), "unit": "butterflies/s",
                         "frac": round(bfly_s / peak, 4), "peak_source": "tools/modmul_peak.cu run in this process' box (register-resident butterflies)"}
-        out.append({"n": n, "limbs": depth, "crt_bits": bits, "word_bytes": W, "polys": P, "ms_roundtrip": round(ms, 4), "int_roofline": int_roof,
-                    "gcoeff_per_s_per_direction": round(2 * coeffs / (ms * 1e-3) / 1e9, 2),
-                    "butterflies_per_s": round(2 * coeffs / 2 * (n.bit_length() - 1) / (ms * 1e-3), 0),
-                    "roofline": {"bound": "hbm", "achieved": round(gbs, 1), "peak": hbm_peak, "unit": "GB/s",
-                                 "frac": round(gbs / hbm_peak, 4), "traffic": None}})
+        tr = traffic.get((n, depth, bits))
+        roof = {"bound": "hbm", "achieved": round(gbs, 1), "peak": hbm_peak, "unit": "GB/s", "frac": round(gbs / hbm_peak, 4),
+                "traffic": int(tr["dram_bytes_per_roundtrip"] * (coeffs / tr["coeffs"])) if tr else None, "algorithmic_bytes": algo_bytes}
+        if tr:
+            roof["traffic_source"] = "ncu dram__bytes_read.sum + dram__bytes_write.sum of the forward + inverse launches (profiles/r02_ntt_traffic.json), scaled to this batch"
+        out.append({"n": n, "limbs": depth, "crt_bits": bits, "word_bytes": W, "polys": P, "ms_roundtrip": round(ms, 4), "launches_per_roundtrip": int(launches),
+                    "int_roofline": int_roof, "gcoeff_per_s_per_direction": round(2 * coeffs / (ms * 1e-3) / 1e9, 2),
+                    "butterflies_per_s": round(bfly_s, 0), "roofline": roof,
+                    "best_frac": round(max(gbs / hbm_peak, int_roof["frac"] if int_roof else 0.0), 4)})
         # data must survive the round trip bit for bit (size-independent property at full size)
-        back = m.to_rns()
-        assert np.array_equal(back, host), "NTT round trip changed the data"
-        del m, params
+        assert m == ref, "NTT round trip changed the data"
+        del m, ref, params
     return out
 
 
-def bench_mul_decompose(device, steps, warmup, hbm_peak, ip=None):
-    """configs[2] (C3-a): S(1x30) * G^-1(other 1x30), n=2^14, 15x24-bit limbs, base 2^12."""
+def bench_mul_decompose(cfg, device, steps, warmup, hbm_peak, ip=None):
+    """configs[2] (C3-a/b/c): S(r x d*ell) * G^-1(other d x c) through the fused entry point, with the oracle beside it."""
     from mxx_b200 import GpuDCRTPolyMatrix, ffi
 
-    cfg = C3A
     params, moduli = make_params(cfg, device)
     n, Lm = cfg["n"], cfg["depth"]
-    dpt = -(-cfg["bits"] // cfg["bb"])
+    W = 4 if max(moduli) < (1 << 30) else 8
+    dpt = -(-max(q.bit_length() for q in moduli) // cfg["bb"])
     ell = dpt * Lm
     m_in = cfg["d"] * ell
     S = np.empty((cfg["r"], m_in, Lm, n), dtype=np.uint64)
@@ -266,95 +303,175 @@ def bench_mul_decompose(device, steps, warmup, hbm_peak, ip=None):
         ffi.check_status(L.gpu_matrix_mul_decompose(out.raw, gS.raw, gO.raw, cfg["bb"], 0), "gpu_matrix_mul_decompose")
 
     ms = timed(params, LocalDist(), step, steps, warmup) / steps
-    t0 = time.perf_counter()
-    seq = gS.mul_decompose(gO, fused=False)
-    params.synchronize()
-    seq_ms = (time.perf_counter() - t0) * 1e3
-    assert seq == out, "fused mul_decompose differs from the reference call sequence"
-    W = 4
+    res = {"workload": f"{cfg['name']} mul_decompose S({cfg['r']}x{m_in})*G^-1({cfg['d']}x{cfg['c']}) n=2^{n.bit_length() - 1} L={Lm}x{cfg['bits']}-bit bb={cfg['bb']}",
+           "ms_fused": round(ms, 4), "mul_decompose_per_s": round(1e3 / ms, 2)}
+    if cfg["name"] == "C3-a":
+        t0 = time.perf_counter()
+        seq = gS.mul_decompose(gO, fused=False)
+        params.synchronize()
+        res["ms_reference_call_sequence"] = round((time.perf_counter() - t0) * 1e3, 3)
+        assert seq == out, "fused mul_decompose differs from the reference call sequence"
+        del seq
     logn = n.bit_length() - 1
-    butterflies = (cfg["d"] * cfg["c"] * Lm + m_in * cfg["c"] * Lm) * (n // 2) * logn
+    fwd_b = m_in * cfg["c"] * Lm * (n // 2) * logn
+    inv_b = cfg["d"] * cfg["c"] * Lm * (n // 2) * logn
     macs = cfg["r"] * m_in * cfg["c"] * Lm * n
     min_bytes = W * Lm * n * (cfg["r"] * m_in + cfg["d"] * cfg["c"] + cfg["r"] * cfg["c"])
-    res = {"workload": "C3-a mul_decompose S(1x30)*G^-1(1x30) n=2^14 L=15x24-bit bb=12", "ms_fused": round(ms, 4),
-           "mul_decompose_per_s": round(1e3 / ms, 2), "ms_reference_call_sequence": round(seq_ms, 3),
-           "modmul_per_s": round((butterflies + macs) / (ms * 1e-3), 0), "butterflies": butterflies, "macs": macs,
-           "min_hbm_bytes": min_bytes, "hbm_frac_of_min_bytes": round(min_bytes / (ms * 1e-3) / 1e9 / hbm_peak, 4)}
+    res.update({"modmul_per_s": round((fwd_b + inv_b + macs) / (ms * 1e-3), 0), "butterflies": fwd_b + inv_b, "macs": macs,
+                "min_hbm_bytes": min_bytes, "hbm_frac_of_min_bytes": round(min_bytes / (ms * 1e-3) / 1e9 / hbm_peak, 4)})
     if ip and "bfly_fwd_u32_nocsub" in ip:
-        fwd_b = m_in * cfg["c"] * Lm * (n // 2) * logn
-        inv_b = cfg["d"] * cfg["c"] * Lm * (n // 2) * logn
-        ideal_s = fwd_b / ip["bfly_fwd_u32_nocsub"] + inv_b / ip["bfly_inv_u32"] + macs / ip["mac_u32"]
-        res["int_roofline"] = {"bound": "int-issue", "ideal_ms": round(ideal_s * 1e3, 4), "frac": round(ideal_s / (ms * 1e-3), 4),
-                               "how": "butterflies / measured butterfly peak + MACs / measured MAC peak (tools/modmul_peak.cu), divided by the measured time"}
-    # CPU baseline on a bounded sample (2 of the 30 columns), all host threads, and a parity check of those columns
+        f64 = W == 8 and max(moduli) < (1 << 51)
+        if W == 4:
+            nocsub = max(moduli) * 36 < (1 << 32)
+            fwd_keys, ki, km = ["bfly_fwd_u32_nocsub", "bfly_fwd_u32"] if nocsub else ["bfly_fwd_u32"], "bfly_inv_u32", "mac_u32"
+        else:
+            fwd_keys, ki, km = ["bfly_fwd_f64" if f64 else "bfly_fwd_u64_nocsub"], "bfly_inv_f64" if f64 else "bfly_inv_u64", "mac_u64"
+        fr = {}
+        for kf in fwd_keys:  # the kernel's own forward butterfly first; the faster of the two measured peaks beside it
+            ideal_s = fwd_b / ip[kf] + inv_b / ip[ki] + macs / ip[km]
+            fr[kf] = {"ideal_ms": round(ideal_s * 1e3, 4), "frac": round(ideal_s / (ms * 1e-3), 4)}
+        res["int_roofline"] = {"bound": "fp64-issue" if f64 else "int-issue", "ideal_ms": fr[fwd_keys[0]]["ideal_ms"], "frac": fr[fwd_keys[0]]["frac"],
+                               "against_each_forward_peak": fr,
+                               "how": "butterflies / measured butterfly peak + MACs / measured MAC peak (tools/modmul_peak.cu), divided by the measured time; "
+                                      + ("mac_u64 is the integer MAC: the FP64 product kernel is not in the microbenchmark" if f64 else "the first key is the butterfly this kernel runs")}
+    # CPU baseline on a bounded sample (oracle_cols of the columns), all host threads, and a parity check of those columns
     from oracle import oracle as orc
 
+    orc.lib().orc_set_threads(host_threads())
     plan = orc.Plan(n, moduli)
+    k = cfg["oracle_cols"]
     t0 = time.perf_counter()
-    cpu = plan.mul_decompose(S, O[:, :2], cfg["bb"])
+    cpu = plan.mul_decompose(S, O[:, :k], cfg["bb"])
     dt = time.perf_counter() - t0
-    assert np.array_equal(cpu, out.to_rns()[:, :2]), "GPU mul_decompose differs from the CPU oracle"
-    res["cpu_baseline"] = {"value": round(1.0 / (dt * cfg["c"] / 2), 4), "unit": "mul_decompose/s", "cores": orc.lib().orc_get_threads(),
-                           "kind": "port", "sample": "2 of the 30 columns (oracle/dcrt_oracle.c orc_mul_decompose), scaled by 15",
-                           "parity": "bit-exact vs GPU result on the sampled columns"}
+    assert np.array_equal(cpu, out.to_rns()[:, :k]), "GPU mul_decompose differs from the CPU oracle"
+    res["cpu_baseline"] = {"value": round(1.0 / (dt * cfg["c"] / k), 4), "unit": "mul_decompose/s", "cores": orc.lib().orc_get_threads(),
+                           "kind": "port", "sample": f"{k} of the {cfg['c']} columns (oracle/dcrt_oracle.c orc_mul_decompose), scaled by {cfg['c'] / k:g}",
+                           "parity": f"bit-exact vs GPU result on {'all' if k == cfg['c'] else 'the sampled'} columns"}
     return res
 
 
-def bench_bgg_chain(dist, device, depth_gates=8):
-    """configs[3] (C4): depth-8 chain of BGG+ encoding products at n = 2^15 (L = 8 x 51-bit, base 2^17, d = 1), the
-    columns of every right operand sharded over the ranks; per gate one fused mul_decompose on the local columns
-    (no collective) and ONE all-gather of the stacked (1 + d) x m block (mxx_b200/bgg.py, mxx_b200/dist.py).
-    The encoding relation c = s*A - x*(s*G) is checked on the final encoding (exact, error-free inputs)."""
-    from mxx_b200 import GpuDCRTPolyMatrix, GpuDCRTPolyParams, standard_moduli
-    from mxx_b200.bgg import BggEncoding, BggPublicKey, ShardedBggEvaluator, encode
-    from mxx_b200.dist import ColumnShardedOps, ColumnShards
+def bench_small_products(device, steps, warmup):
+    """configs[0] (C1-J): the reference's CPU-runnable case, small square matrices at n = 2^12 with 4 x 50-bit limbs
+    (benches/bench_matrix_mul_cpu.rs:17-20), `steps` products back to back per timing, checked against the oracle."""
+    from mxx_b200 import GpuDCRTPolyMatrix, ffi
+    from oracle import oracle as orc
 
-    n, Lm, bits, bb, d = 1 << 15, 8, 51, 17, 1
+    orc.lib().orc_set_threads(host_threads())
+    rows = []
+    L = ffi.lib()
+    for cfg in C1J:
+        params, moduli = make_params(cfg, device)
+        plan = orc.Plan(cfg["n"], moduli)
+        A, B = plan.uniform(cfg["r"], cfg["k"], seed=0x6D7878_0301), plan.uniform(cfg["k"], cfg["c"], seed=0x6D7878_0302)
+        gA, gB = GpuDCRTPolyMatrix.from_rns(params, A), GpuDCRTPolyMatrix.from_rns(params, B)
+        gO = GpuDCRTPolyMatrix(params, cfg["r"], cfg["c"])
+
+        def step():
+            ffi.check_status(L.gpu_matrix_mul(gO.raw, gA.raw, gB.raw), "gpu_matrix_mul")
+
+        ms = timed(params, LocalDist(), step, max(steps, 20), warmup) / max(steps, 20)
+        t0 = time.perf_counter()
+        want = plan.mul(A, B)
+        cpu_s = time.perf_counter() - t0
+        assert np.array_equal(gO.to_rns(), want), "GPU small product differs from the CPU oracle"
+        W, Lm, n = 8, cfg["depth"], cfg["n"]
+        algo = W * Lm * n * (cfg["r"] * cfg["k"] + cfg["k"] * cfg["c"] + cfg["r"] * cfg["c"])
+        rows.append({"workload": f"{cfg['name']} mul n=2^12 L=4x50-bit", "ms": round(ms, 5), "matrix_muls_per_s": round(1e3 / ms, 1),
+                     "algorithmic_gbs": round(algo / (ms * 1e-3) / 1e9, 1), "note": "operands fit the L2; launch latency and integer issue bound",
+                     "cpu_baseline": {"value": round(1.0 / cpu_s, 2), "unit": "matrix-muls/s", "cores": orc.lib().orc_get_threads(), "kind": "port",
+                                      "sample": "one full product", "parity": "bit-exact vs GPU result"}})
+    return rows
+
+
+def bench_bgg_chain(dist, device, cfg, depth_gates=8):
+    """configs[3] (C4): depth-8 chain of BGG+ encoding products at n = 2^15, d = 1, on stacked encodings (mxx_b200/bgg.py):
+    per gate ONE fused mul_decompose sharing G^-1(A_y) between the vector and the public key, the `+ c_y x` tail in place,
+    and the exchange the partition needs.  Timed on ONE device (every rank runs it at the same time: `n1`) and on every
+    partition of the ranks into (limb groups x column blocks): columns only = one in-place all-gather of the (1+d) x m result
+    per gate; limbs only = one all-gather of the coefficient-form A_y block per gate, the result stays limb-sharded.
+    The encoding relation c = s*A - x*(s*G) is checked on the final encoding of every partition (exact, error-free inputs)."""
+    from mxx_b200 import GpuDCRTPolyMatrix as M, GpuDCRTPolyParams, standard_moduli
+    from mxx_b200.bgg import BggPublicKey, GridBggEvaluator, ShardedBggEvaluator, StackedEncoding, encode
+    from mxx_b200.dist import GridShardedOps, LocalOps
+
+    n, Lm, bits, bb, d = cfg["n"], cfg["depth"], cfg["bits"], cfg["bb"], cfg["d"]
     moduli = standard_moduli(n, Lm, bits)
     params = GpuDCRTPolyParams(n, moduli, bb, gpu_ids=(device,))
-    ell = params.modulus_digits()
-    m = d * ell
-    ops = ColumnShardedOps(params) if dist.world > 1 else None
+    m = d * params.modulus_digits()
+    runs_n = int(os.environ.get("MXX_BENCH_CHAIN_RUNS", "5"))  # host-timed: the median of five chains keeps a host hiccup out of the record
 
     def rnd(rows, cols, seed):
         h = np.empty((rows, cols, Lm, n), dtype=np.uint64)
         uniform_host(h, moduli, seed=seed)
-        return GpuDCRTPolyMatrix.from_rns(params, h, True)
+        return M.from_rns(params, h, True)
 
-    gadget = GpuDCRTPolyMatrix.gadget_matrix(params, d)
+    gadget = M.gadget_matrix(params, d)
     secret = rnd(1, d, 0x6D7878_0200)
     left = encode(secret, BggPublicKey(rnd(d, m, 0x6D7878_0201)), rnd(1, 1, 0x6D7878_0202), gadget)
     right = encode(secret, BggPublicKey(rnd(d, m, 0x6D7878_0203)), rnd(1, 1, 0x6D7878_0204), gadget)
-    sh = ColumnShards(m, dist.world)
-    c0, c1 = sh.range(dist.rank)
-    r_vec_local, r_pk_local = right.vector.slice_columns(c0, c1), right.pubkey.matrix.slice_columns(c0, c1)
-    ev = ShardedBggEvaluator(ops) if ops else None
+    sg = secret * gadget
 
-    def gate(acc):
-        if ev:
-            return ev.mul_gate(acc, r_vec_local, r_pk_local, right.plaintext, m)
-        return acc.mul(right, fused=True)
+    def run_chain(ev, start, rv, rp, rx, sync):
+        acc = ev.mul_gate_stacked(start, rv, rp, rx, m)  # warm-up (communicators, pools)
+        runs = []
+        for _ in range(runs_n):
+            sync()
+            dist.barrier()
+            t0 = time.perf_counter()
+            acc = start
+            for _ in range(depth_gates):
+                acc = ev.mul_gate_stacked(acc, rv, rp, rx, m)
+            sync()
+            runs.append(dist.max(time.perf_counter() - t0))
+        return acc, sorted(runs)[len(runs) // 2], runs
 
-    acc = gate(left)  # warm-up (NCCL communicator, pools)
-    runs = []
-    for _ in range(int(os.environ.get("MXX_BENCH_CHAIN_RUNS", "5"))):  # the chain is host-timed: the median of five runs keeps a host hiccup out of the record
-        params.synchronize()
-        dist.barrier()
-        t0 = time.perf_counter()
-        acc = left
-        for _ in range(depth_gates):
-            acc = gate(acc)
-        params.synchronize()
-        runs.append(dist.max(time.perf_counter() - t0))
-    dt = sorted(runs)[len(runs) // 2]
-    ok = acc.vector == secret * acc.pubkey.matrix - (secret * gadget).mul_scalar(acc.plaintext)
-    logn = 15
-    per_gate_bfly = (d * m * Lm + m * m * Lm) * (n // 2) * logn
-    return {"workload": "C4 BGG+ encoding-product chain, n=2^15, L=8x51-bit, bb=17 (ell=24), d=1, depth 8; right-operand columns sharded over the ranks",
-            "gates": depth_gates, "ms_per_gate": round(dt * 1e3 / depth_gates, 4), "gates_per_s": round(depth_gates / dt, 2),
-            "butterflies_per_gate": per_gate_bfly, "exchange": "one all_gather of the (1+d) x m block per gate" if ev else "none (1 rank)",
-            "relation_holds": bool(ok), "ms_per_gate_runs": [round(r * 1e3 / depth_gates, 4) for r in runs],
-            "timing": "host clock around the chain with a stream synchronize and barrier on both sides, max over ranks; median of the chains in ms_per_gate_runs"}
+    def relation(acc, sec, sgad):
+        st = acc.stacked
+        vec, pk = st.slice_rows(0, acc.vec_rows), st.slice_rows(acc.vec_rows, st.nrow)
+        return bool(vec == sec * pk - sgad.mul_scalar(acc.plaintext))
+
+    # ---- one device ---------------------------------------------------------------------------------------------------
+    start = StackedEncoding.from_encoding(left)
+    acc, dt1, runs1 = run_chain(ShardedBggEvaluator(LocalOps(params)), start, right.vector, right.pubkey.matrix, right.plaintext, params.synchronize)
+    ok1 = relation(acc, secret, sg)
+    logn = n.bit_length() - 1
+    res = {"workload": f"{cfg['name']} BGG+ encoding-product chain, n=2^{logn}, bb={bb} (ell={m // d}), d={d}, depth {depth_gates}",
+           "gates": depth_gates, "butterflies_per_gate": (d * m * Lm + m * m * Lm) * (n // 2) * logn,
+           "n1": {"ms_per_gate": round(dt1 * 1e3 / depth_gates, 4), "gates_per_s": round(depth_gates / dt1, 2), "relation_holds": ok1,
+                  "ms_per_gate_runs": [round(r * 1e3 / depth_gates, 4) for r in runs1],
+                  "what": "the whole chain on one device" + (" (every rank runs it at the same time; max over ranks)" if dist.world > 1 else "")},
+           "timing": "host clock around the chain with a stream synchronize and barrier on both sides, max over ranks; median of the chains in ms_per_gate_runs"}
+    res["ms_per_gate"], res["gates_per_s"], res["relation_holds"] = res["n1"]["ms_per_gate"], res["n1"]["gates_per_s"], ok1
+    if dist.world == 1:
+        return res
+    # ---- every (limb groups x column blocks) partition of the ranks --------------------------------------------------------
+    host = {"st": start.stacked.to_rns(), "lx": left.plaintext.to_rns(), "rv": right.vector.to_rns(), "rp": right.pubkey.matrix.to_rns(),
+            "rx": right.plaintext.to_rns(), "sec": secret.to_rns(), "sg": sg.to_rns()}
+    del acc, start, left, right, gadget, secret, sg
+    parts = []
+    for lg in (1, 2, 4, 8, 16):
+        if lg > dist.world or dist.world % lg or Lm % lg or m % (dist.world // lg):
+            continue
+        cg = dist.world // lg
+        g = GridShardedOps(n, moduli, bb, lg, cg, device=device)
+        up = lambda h, sharded: M.from_rns(g.params, g.grid.slice_host(h, dist.rank, ncol_sharded=sharded), True)  # noqa: E731
+        st0 = StackedEncoding(up(host["st"], False), 1, up(host["lx"], False))
+        acc, dt, runs = run_chain(GridBggEvaluator(g), st0, up(host["rv"], True), up(host["rp"], True), up(host["rx"], False), g.params.synchronize)
+        ok = dist.max(0.0 if relation(acc, up(host["sec"], False), up(host["sg"], False)) else 1.0) == 0.0
+        exch = []
+        if lg > 1:
+            exch.append(f"all-gather of the coefficient-form A_y block along the limb axis ({lg} ranks)")
+        if cg > 1:
+            exch.append(f"in-place all-gather of the (1+d) x m result rows along the column axis ({cg} ranks)")
+        parts.append({"limb_groups": lg, "col_groups": cg, "ms_per_gate": round(dt * 1e3 / depth_gates, 4), "gates_per_s": round(depth_gates / dt, 2),
+                      "speedup_vs_n1": round(dt1 / dt, 3), "relation_holds": bool(ok), "exchange_per_gate": exch,
+                      "ms_per_gate_runs": [round(r * 1e3 / depth_gates, 4) for r in runs]})
+        del acc, st0, g
+    best = min(parts, key=lambda p: p["ms_per_gate"])
+    res.update({"partitions": parts, "best_partition": f"{best['limb_groups']} limb groups x {best['col_groups']} column blocks",
+                "ms_per_gate": best["ms_per_gate"], "gates_per_s": best["gates_per_s"], "speedup_vs_n1": best["speedup_vs_n1"],
+                "relation_holds": bool(ok1 and all(p["relation_holds"] for p in parts))})
+    return res
 
 
 def bench_preimage(device, steps, warmup):
@@ -455,6 +572,7 @@ def cpu_matmul_baseline(A, B, moduli, n, reps):
     """the oracle port of the reference CPU loop (src/matrix/base/memory.rs:589-605), all host threads"""
     from oracle import oracle as orc
 
+    orc.lib().orc_set_threads(host_threads())
     plan = orc.Plan(n, moduli)
     threads = orc.lib().orc_get_threads()
     plan.mul(A[:, :2], B[:2, :4])  # warm-up on a corner
@@ -522,31 +640,41 @@ def run_gpu(args):
     e2e_value = dist.world * e2e_steps / e2e_s
     result_host = pinO.array.copy()
 
-    # ---- assembly (N > 1): one NCCL all-gather of the ranks' output column blocks, timed on its own -------------
+    # ---- assembly (N > 1): the ranks' output column blocks all-gathered IN PLACE into the r x 120N result (one ncclAllGather per
+    # row straight into the result's storage, mxx_b200/dist.py), timed (a) inside the step and (b) on its own ----------------
     assemble = None
     if dist.world > 1:
-        from mxx_b200.dist import ColumnShardedOps
+        from mxx_b200.dist import ColumnShardedOps, ColumnShards, all_gather_columns_into
 
         ops = ColumnShardedOps(params)
-        ops.all_gather_columns(gO, c * dist.world)  # warm-up (NCCL communicator setup)
-        params.synchronize()
-        dist.barrier()
-        t0 = time.perf_counter()
-        full = ops.all_gather_columns(gO, c * dist.world)
-        params.synchronize()
-        asm_s = dist.max(time.perf_counter() - t0)
+        full = GpuDCRTPolyMatrix(params, r, c * dist.world)
+        sh = ColumnShards(c * dist.world, dist.world)
+
+        def gather():
+            with ops._stream():
+                all_gather_columns_into(full, gO, sh, dist.rank, None)
+
+        def step_assembled():
+            step()
+            gather()
+
+        asm_total = timed(params, dist, step_assembled, args.steps, args.warmup)
+        gather_total = timed(params, dist, gather, args.steps, args.warmup)
         nbytes = r * c * dist.world * Lm * n * 4
-        assemble = {"ms": round(asm_s * 1e3, 3), "bytes_assembled_per_rank": nbytes,
-                    "what": "all_gather of the r x 120 output blocks into the r x 120N result on every rank (mxx_b200/dist.py); not part of `value`"}
+        gms = gather_total / args.steps
+        assemble = {"value_assembled": round(dist.world * 1e3 / (asm_total / args.steps), 2), "ms_per_step_assembled": round(asm_total / args.steps, 4),
+                    "ms": round(gms, 4), "bytes_assembled_per_rank": nbytes, "landing_gbs_per_rank": round(nbytes * (dist.world - 1) / dist.world / (gms * 1e-3) / 1e9, 1),
+                    "what": "value_assembled = 120-column products per second when every step also all-gathers the r x 120 output blocks into the "
+                            "r x 120N result on every rank (in place, CUDA events on the context stream, max over ranks); ms = the all-gather alone"}
+        # the assembled result holds every rank's block: spot-check this rank's own block and its neighbour's shape
+        assert full.slice_columns(c * dist.rank, c * (dist.rank + 1)) == gO, "assembled block differs from the local product"
         del full
 
     line = {
         "metric": "DCRT matrix-muls/s", "value": round(value, 2), "unit": "matrix-muls/s", "n_gpus": dist.world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-        "config": {"workload": "C1-R bench_matrix_mul: DCRTPolyMatrix 1x30 * 30x120, n=2^14, 15 CRT limbs x 24 bit, EVAL operands "
-                               "(benches/bench_matrix_mul_cpu.rs:10-16)", "ring_dim": n, "limbs": Lm, "crt_bits": cfg["bits"],
-                   "shape": [r, k, c], "per_gpu": "column block: A 1x30 replicated, each rank owns 120 columns of B and of the result (job = 1x30 * 30x(120*N)); value counts 120-column products", "l2": "inputs (3.57 GB) exceed the 126 MB L2"},
+        "config": c1r_config(),
         "e2e": {"value": round(e2e_value, 3), "unit": "matrix-muls/s", "h2d_bytes_per_step": int(pinA.nbytes + pinB.nbytes),
                 "d2h_bytes_per_step": int(pinO.nbytes), "steps": e2e_steps,
                 "path": "gpu_matrix_load_rns_batch x2 (pinned host u64) -> gpu_matrix_mul -> gpu_matrix_store_rns_batch -> gpu_event_set_wait"},
@@ -557,10 +685,15 @@ def run_gpu(args):
                      "peak_source": peak_src + "; a copy moves read+write, this kernel is 97% reads, so a fraction slightly above 1 is expected"},
         "clocks": clk.summary(),
     }
+    line["e2e"]["bound"] = ("host memory bandwidth + PCIe: 7.14 GB of u64 host words per step (the ABI fixes the host layout); floor ~65 ms "
+                            "if every word were narrowed at ~55 GB/s (DESIGN.md 7); not a kernel number")
     if assemble:
         line["assemble"] = assemble
+        line["value_assembled"] = assemble["value_assembled"]
     if not args.no_extras:
-        line["bgg_chain"] = bench_bgg_chain(dist, device)
+        chains = [bench_bgg_chain(dist, device, cfg4) for cfg4 in C4]
+        line["bgg_chain"] = chains[0]
+        line["bgg_chain_28bit"] = chains[1]
 
     if dist.rank == 0 and dist.world == 1:
         # CPU baseline beside it: same operands, all host threads, and a parity check of the GPU result
@@ -580,7 +713,10 @@ def run_gpu(args):
             ip = int_peaks()
             line["int_peaks"] = ip
             line["ntt"] = bench_ntt(device, max(3, min(args.steps, 20)), args.warmup, hbm_peak, ip)
-            line["mul_decompose"] = bench_mul_decompose(device, max(3, min(args.steps, 20)), args.warmup, hbm_peak, ip)
+            md = [bench_mul_decompose(cfg3, device, max(3, min(args.steps, 20)), args.warmup, hbm_peak, ip) for cfg3 in C3]
+            line["mul_decompose"] = md[0]
+            line["mul_decompose_c3b"], line["mul_decompose_c3c"] = md[1], md[2]
+            line["small_products"] = bench_small_products(device, args.steps, args.warmup)
             line["preimage"] = bench_preimage(device, args.steps, args.warmup)
     if dist.rank == 0:
         emit(line)
@@ -589,7 +725,9 @@ def run_gpu(args):
 
 def run_reference(args):
     """reference arm: the reference's CPU algorithm for the same workload on the host cores.
-    OpenFHE / cargo are absent, so this is the oracle port; rank 0 only."""
+    OpenFHE / cargo are absent, so this is the oracle port; rank 0 only.  Same operands (seeds) as rank 0 of
+    the GPU arm, the driver's steps and warm-up, every core this process may use (set explicitly: torchrun exports
+    OMP_NUM_THREADS=1), the same `config` object."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
     from mxx_b200.params import standard_moduli
@@ -600,12 +738,13 @@ def run_reference(args):
     A = np.empty((r, k, Lm, n), dtype=np.uint64)
     B = np.empty((k, c, Lm, n), dtype=np.uint64)
     uniform_host(A, moduli, seed=0x6D7878_0001)
-    uniform_host(B, moduli, seed=0x6D7878_0002)
+    uniform_host(B, moduli, seed=0x6D7878_0100)
     from oracle import oracle as orc
 
+    orc.lib().orc_set_threads(host_threads())
     plan = orc.Plan(n, moduli)
     threads = orc.lib().orc_get_threads()
-    steps, warmup = min(args.steps, 20), min(args.warmup, 3)
+    steps, warmup = args.steps, args.warmup
     for _ in range(warmup):
         plan.mul(A, B)
     t0 = time.perf_counter()
@@ -615,9 +754,7 @@ def run_reference(args):
     v = round(1.0 / dt, 4)
     line = {"impl": "reference", "metric": "DCRT matrix-muls/s", "value": v, "unit": "matrix-muls/s", "n_gpus": args.gpus,
             "steps": steps, "warmup": warmup, "ms_per_step": round(dt * 1e3, 3), "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-            "config": {"workload": "C1-R bench_matrix_mul: DCRTPolyMatrix 1x30 * 30x120, n=2^14, 15 CRT limbs x 24 bit, EVAL operands "
-                                   "(benches/bench_matrix_mul_cpu.rs:10-16)", "ring_dim": n, "limbs": Lm, "crt_bits": cfg["bits"], "shape": [r, k, c]},
+            "vs_baseline": None, "dtype": "u64", "data": "synthetic", "config": c1r_config(),
             "cpu_baseline": {"value": v, "unit": "matrix-muls/s", "cores": threads, "kind": "port",
                              "sample": f"the full C1-R product, {steps} timed steps (oracle port of src/matrix/base/memory.rs:589-605; "
                                        "the reference's own OpenFHE path is unavailable on this box)"},
@@ -653,7 +790,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg (profiling runs)")
     ap.add_argument("--no-extras", action="store_true", help="skip the NTT and mul_decompose sections (profiling runs)")
     args = ap.parse_args()
-    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    args.warmup = max(args.warmup, 3)  # both arms: the timing rules ask for at least three warm-up steps
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -331,8 +331,20 @@ struct DecompGeom {
     uint32_t gathered;
     uint32_t src_tpg;
     unsigned long long src_group_stride, src_poly_stride;
-    unsigned char tower_bits[64];
+    unsigned long long tb0, tb1, tb2, tb3, tb4, tb5, tb6, tb7;  // 8 bits per tower, tower t in word t / 8 (see tower_bits_of)
 };
+// bit width of source tower t of a gathered source.  The word is selected by compares on named fields: a dynamic index
+// into a kernel parameter makes the compiler copy the whole geometry to local memory (a 120-byte stack frame).
+GP_HD uint32_t tower_bits_of(const DecompGeom &g, uint32_t t) {
+    const uint32_t i = t >> 3;
+    const unsigned long long lo = i < 2 ? (i == 0 ? g.tb0 : g.tb1) : (i == 2 ? g.tb2 : g.tb3);
+    const unsigned long long hi = i < 6 ? (i == 4 ? g.tb4 : g.tb5) : (i == 6 ? g.tb6 : g.tb7);
+    return (uint32_t)((i < 4 ? lo : hi) >> ((t & 7) * 8)) & 0xffu;
+}
+GP_HD void set_tower_bits(DecompGeom &g, uint32_t t, uint32_t bits) {
+    unsigned long long *w[8] = {&g.tb0, &g.tb1, &g.tb2, &g.tb3, &g.tb4, &g.tb5, &g.tb6, &g.tb7};
+    *w[(t >> 3) & 7] |= (unsigned long long)(bits & 0xffu) << ((t & 7) * 8);
+}
 // Where one output (poly, limb) of a decomposition reads its digits: source offset (words), shift and bit count of the
 // digit (0 bits: the digit is zero), output limb.  Row order row*ell + t*dpt + dg with the narrowed last digit of a
 // tower (cuda/src/matrix/MatrixDecompose.cu:93-113).
@@ -351,7 +363,7 @@ GP_HD DigitSpec digit_spec(const DecompGeom &g, size_t pl, uint32_t logn, const 
     const size_t spoly = row * g.src_cols + g.src_col0 + col;
     uint32_t sbits;
     if (g.gathered) {
-        sbits = g.tower_bits[t & 63];
+        sbits = tower_bits_of(g, t);
         d.soff = (size_t)(t / g.src_tpg) * g.src_group_stride + spoly * g.src_poly_stride + ((size_t)(t % g.src_tpg) << logn);
     } else {
         sbits = lc[t].bits;

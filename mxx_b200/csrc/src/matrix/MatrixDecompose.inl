@@ -109,7 +109,7 @@ int run_decompose(GpuContext *ctx, const T *src_coeff, T *out, size_t rows, size
         g.src_tpg = gs->tpg;
         g.src_group_stride = gs->group_stride;
         g.src_poly_stride = gs->poly_stride;
-        memcpy(g.tower_bits, gs->bits, sizeof(g.tower_bits));
+        for (uint32_t t = 0; t < gs->towers && t < 64; t++) gp::set_tower_bits(g, t, gs->bits[t]);
     }
     const size_t opl = rows * g.ell * cols * limbs;
     if (opl == 0) return 0;

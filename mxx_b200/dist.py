@@ -134,6 +134,28 @@ def all_gather_columns_into(out: GpuDCRTPolyMatrix, local: GpuDCRTPolyMatrix, sh
             out.copy_block_from(recv, 0, c0, r * local.nrow, 0, local.nrow, c1 - c0)
 
 
+class LocalOps:
+    """The degenerate partition: one device owns everything (the evaluators in mxx_b200/bgg.py take any of the three)."""
+
+    rank, world = 0, 1
+
+    def __init__(self, params):
+        self.params = params
+
+    def shards(self, ncol: int) -> ColumnShards:
+        return ColumnShards(ncol, 1)
+
+    def mul(self, lhs, rhs_local):
+        return lhs * rhs_local
+
+    def mul_decompose(self, lhs, other_local, fused: bool = True):
+        return lhs.mul_decompose(other_local, fused=fused)
+
+    def all_gather_columns(self, local, ncol: int):
+        assert local.ncol == ncol
+        return local
+
+
 class ColumnShardedOps:
     """The hot path on this rank's column block + the NCCL assembly step."""
 
