@@ -412,15 +412,24 @@ def bench_bgg_chain(dist, device, cfg, depth_gates=8):
     sg = secret * gadget
 
     def run_chain(ev, start, rv, rp, rx, sync):
-        acc = ev.mul_gate_stacked(start, rv, rp, rx, m)  # warm-up (communicators, pools)
+        prefetch = getattr(ev, "prefetch", None)  # limb partitions: the next gate's tower exchange travels under this gate's product
+
+        def chain(gates):
+            acc = start
+            handle = prefetch(rp) if prefetch else None
+            for k in range(gates):
+                nxt = prefetch(rp) if prefetch and k + 1 < gates else None
+                acc = ev.mul_gate_stacked(acc, rv, rp, rx, m, gathered=handle) if prefetch else ev.mul_gate_stacked(acc, rv, rp, rx, m)
+                handle = nxt
+            return acc
+
+        acc = chain(2)  # warm-up (communicators, pools)
         runs = []
         for _ in range(runs_n):
             sync()
             dist.barrier()
             t0 = time.perf_counter()
-            acc = start
-            for _ in range(depth_gates):
-                acc = ev.mul_gate_stacked(acc, rv, rp, rx, m)
+            acc = chain(depth_gates)
             sync()
             runs.append(dist.max(time.perf_counter() - t0))
         return acc, sorted(runs)[len(runs) // 2], runs
@@ -460,7 +469,7 @@ def bench_bgg_chain(dist, device, cfg, depth_gates=8):
         ok = dist.max(0.0 if relation(acc, up(host["sec"], False), up(host["sg"], False)) else 1.0) == 0.0
         exch = []
         if lg > 1:
-            exch.append(f"all-gather of the coefficient-form A_y block along the limb axis ({lg} ranks)")
+            exch.append(f"in-place all-gather of the coefficient-form A_y block along the limb axis ({lg} ranks), started one gate ahead (asynchronous)")
         if cg > 1:
             exch.append(f"in-place all-gather of the (1+d) x m result rows along the column axis ({cg} ranks)")
         parts.append({"limb_groups": lg, "col_groups": cg, "ms_per_gate": round(dt * 1e3 / depth_gates, 4), "gates_per_s": round(depth_gates / dt, 2),
@@ -779,6 +788,9 @@ def emit(line: dict) -> None:
 
 def main():
     global _REAL_STDOUT
+    import faulthandler
+
+    faulthandler.enable()  # a native crash in one rank leaves its Python stack on stderr
     sys.stdout.flush()
     _REAL_STDOUT = os.dup(1)
     os.dup2(2, 1)  # fd 1 -> stderr for the duration of the run

@@ -138,6 +138,9 @@ int gpu_matrix_mul_decompose(GpuMatrix *out, const GpuMatrix *lhs, const GpuMatr
 int gpu_matrix_mul_decompose_gathered(GpuMatrix *out, const GpuMatrix *lhs, const void *other_coeff, size_t d, size_t c, size_t col0,
                                       const uint64_t *tower_moduli, size_t towers, size_t towers_per_group,
                                       size_t group_stride_words, size_t poly_stride_words, uint32_t base_bits, int small);
+/* rows [dst_row, dst_row + src->rows) of dst <- coefficient form of src (src EVAL or COEFF, untouched; dst tagged COEFF): the
+ * inverse transform written straight into this rank's block of the all-gather buffer of a limb-sharded mul_decompose. */
+int gpu_matrix_intt_to(GpuMatrix *dst, size_t dst_row, const GpuMatrix *src);
 /* out[dst block] += src[src block] * scalar (scalar 1x1; all EVAL): the `+ c_y * x` tail of a BGG encoding product
  * (src/bgg/encoding.rs:135) applied in place to the vector rows of a stacked product, one launch. */
 int gpu_matrix_add_scaled_block(GpuMatrix *out, const GpuMatrix *src, const GpuMatrix *scalar, size_t dst_row, size_t dst_col,

@@ -124,17 +124,24 @@ class ShardedBggEvaluator:
 class GridBggEvaluator:
     """The same chain on a 2-D (limb group x column block) partition (mxx_b200.dist.GridShardedOps).  Every matrix
     holds this rank's limbs only; the left encoding has all m columns, the right operands this rank's column block.
-    Per gate: one all-gather of the coefficient-form A_y block along the limb axis (inside mul_decompose), the local
-    product, and — only when the columns are split too — one all-gather of the result rows along the column axis."""
+    Per gate: one all-gather of the coefficient-form A_y block along the limb axis, the local product, and — only when the
+    columns are split too — one all-gather of the result rows along the column axis.
+
+    The limb-axis exchange depends on the RIGHT operand only, and an evaluator knows its wires ahead of time: `prefetch`
+    starts a gate's exchange (inverse transform + asynchronous in-place all-gather) so that it travels while the previous
+    gate's product is computed; `mul_gate_stacked(..., gathered=handle)` then finds the towers already there."""
 
     def __init__(self, ops):
         self.ops = ops
 
+    def prefetch(self, right_pk_local: GpuDCRTPolyMatrix):
+        return self.ops.gather_towers_async(right_pk_local)
+
     def mul_gate_stacked(self, left: StackedEncoding, right_vec_local: GpuDCRTPolyMatrix, right_pk_local: GpuDCRTPolyMatrix,
-                         right_plaintext: GpuDCRTPolyMatrix | None, ncol: int) -> StackedEncoding:
+                         right_plaintext: GpuDCRTPolyMatrix | None, ncol: int, gathered=None) -> StackedEncoding:
         if left.plaintext is None:
             raise ValueError("Unknown plaintext for the left-hand input of multiplication")
-        prod_local = self.ops.mul_decompose(left.stacked, right_pk_local)                   # limb-axis all-gather inside
+        prod_local = self.ops.mul_decompose(left.stacked, right_pk_local, gathered=gathered)  # limb-axis all-gather
         prod_local.add_scaled_block_from(right_vec_local, left.plaintext, 0, 0, 0, 0, left.vec_rows, prod_local.ncol)
         full = self.ops.all_gather_columns(prod_local, ncol)                               # column-axis all-gather
         pt = left.plaintext * right_plaintext if right_plaintext is not None else None

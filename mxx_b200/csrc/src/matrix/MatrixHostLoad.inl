@@ -226,10 +226,12 @@ int load_hybrid(GpuContext *ctx, GpuMatrix *mat, const uint64_t *host, size_t wo
                 sh.cv.notify_all();
             }
             {
+                // notify UNDER the lock: the waiter (drain) owns `sh` on its stack and destroys it as soon as it sees
+                // workers_live == 0, so nothing of `sh` may be touched after the mutex is released
                 std::lock_guard<std::mutex> g(sh.m);
                 sh.workers_live--;
+                sh.cv.notify_all();
             }
-            sh.cv.notify_all();
         });
     }
     // from here on every exit path must wait for the workers (they reference this frame)

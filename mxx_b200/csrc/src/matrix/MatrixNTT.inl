@@ -211,3 +211,25 @@ extern "C" int gpu_matrix_intt_all(GpuMatrix *mat) {
     if (mat->format == GPU_POLY_FORMAT_COEFF) return 0;  // MatrixNTT.cu:806-809
     return matrix_transform(mat, true);
 }
+
+// extension: rows [dst_row, dst_row + src->rows) of dst <- coefficient form of src (src untouched): the inverse transform
+// written straight into its block of an all-gather buffer (limb-sharded mul_decompose, mxx_b200/dist.py gather_towers),
+// instead of clone + intt_all + copy_block.  dst is tagged COEFF.
+extern "C" int gpu_matrix_intt_to(GpuMatrix *dst, size_t dst_row, const GpuMatrix *src) {
+    if (!dst || !src || !dst->ctx) return gp::set_error("invalid gpu_matrix_intt_to arguments");
+    if (dst->ctx != src->ctx || dst->level != src->level) return gp::set_error("context mismatch in gpu_matrix_intt_to");
+    if (dst->cols != src->cols || dst_row + src->rows > dst->rows) return gp::set_error("size mismatch in gpu_matrix_intt_to");
+    if (dst == src || (dst->data && dst->data == src->data)) return gp::set_error("gpu_matrix_intt_to output must not alias the input");
+    dst->format = GPU_POLY_FORMAT_COEFF;
+    if (src->polys() == 0 || src->level < 0) return 0;
+    GpuContext *ctx = dst->ctx;
+    if (bind_device(ctx)) return 1;
+    const uint32_t limbs = (uint32_t)src->limbs();
+    const size_t off = dst_row * dst->cols * src->poly_words();
+    return GP_DISPATCH_WIDTH(
+        ctx, T *d = (T *)dst->data + off; const T *sp = (const T *)src->data;
+        if (src->format == GPU_POLY_FORMAT_COEFF) {
+            GP_CUDA(cudaMemcpyAsync(d, sp, src->bytes(), cudaMemcpyDeviceToDevice, gp::cur(ctx)), "cudaMemcpyAsync(intt_to)");
+            return 0;
+        } return run_ntt_inv<T>(ctx, sp, d, src->polys(), limbs););
+}

@@ -309,31 +309,49 @@ class GridShardedOps:
         return ColumnShards(ncol, self.grid.col_groups)
 
     # -- the limb-axis exchange: coefficient form of the right operand, all towers ---------------------------------
-    def gather_towers(self, other_local: GpuDCRTPolyMatrix) -> GpuDCRTPolyMatrix:
-        """(d x c) on this rank's towers, EVAL or COEFF -> (limb_groups*d x c) COEFF matrix of this rank's context whose
-        rows [g*d, (g+1)*d) hold limb group g's towers (the layout gpu_matrix_mul_decompose_gathered reads)."""
+    def gather_towers_async(self, other_local: GpuDCRTPolyMatrix):
+        """Starts the exchange and returns a handle for `mul_decompose(..., gathered=handle)`.
+
+        (d x c) on this rank's towers, EVAL or COEFF -> (limb_groups*d x c) COEFF matrix of this rank's context whose rows
+        [g*d, (g+1)*d) hold limb group g's towers (the layout gpu_matrix_mul_decompose_gathered reads).  The inverse
+        transform writes this rank's block in place and the all-gather is an IN-PLACE ncclAllGather on that buffer, issued
+        asynchronously: it runs on NCCL's stream while the context stream goes on with whatever is enqueued next (the
+        product of the PREVIOUS gate when an evaluator prefetches its right operands); `wait_towers` joins it."""
         torch, dist = _torch()
-        coeff = other_local
-        if other_local.is_ntt:
-            coeff = other_local.clone()
-            coeff.intt_all_in_place()
-        if self.grid.limb_groups == 1:
-            return coeff if coeff is not other_local else other_local.clone()
-        out = GpuDCRTPolyMatrix(self.params, self.grid.limb_groups * coeff.nrow, coeff.ncol, level=coeff.level, is_ntt=False)
-        with self._stream():
-            dist.all_gather_into_tensor(device_tensor(out), device_tensor(coeff), group=self.limb_group)
+        d = other_local.nrow
+        out = GpuDCRTPolyMatrix(self.params, self.grid.limb_groups * d, other_local.ncol, level=other_local.level, is_ntt=False)
+        out.intt_rows_from(other_local, self.a * d)
+        work = None
+        if self.grid.limb_groups > 1:
+            buf = device_tensor(out)
+            per = buf.numel() // self.grid.limb_groups
+            with self._stream():
+                work = dist.all_gather_into_tensor(buf, buf[self.a * per:(self.a + 1) * per], group=self.limb_group, async_op=True)
+        return (out, work, d)
+
+    def wait_towers(self, handle) -> GpuDCRTPolyMatrix:
+        out, work, _ = handle
+        if work is not None:
+            with self._stream():
+                work.wait()  # the context stream waits for NCCL's stream; the host does not block
         return out
+
+    def gather_towers(self, other_local: GpuDCRTPolyMatrix) -> GpuDCRTPolyMatrix:
+        return self.wait_towers(self.gather_towers_async(other_local))
 
     # -- compute ------------------------------------------------------------------------------------------------------
     def mul(self, lhs_local_limbs: GpuDCRTPolyMatrix, rhs_local: GpuDCRTPolyMatrix) -> GpuDCRTPolyMatrix:
         """this rank's (limbs, columns) of lhs * rhs: limb-local, no exchange"""
         return lhs_local_limbs * rhs_local
 
-    def mul_decompose(self, lhs_local_limbs: GpuDCRTPolyMatrix, other_local: GpuDCRTPolyMatrix, small: bool = False) -> GpuDCRTPolyMatrix:
+    def mul_decompose(self, lhs_local_limbs: GpuDCRTPolyMatrix, other_local: GpuDCRTPolyMatrix | None, small: bool = False,
+                      gathered=None) -> GpuDCRTPolyMatrix:
         """this rank's (limbs, columns) of lhs * G^-1(other): one all-gather of the coefficient-form `other` block along
-        the limb axis, then digits + NTT + MAC on the local limbs (lhs: all columns of S on this rank's limbs)"""
-        gathered = self.gather_towers(other_local)
-        return lhs_local_limbs.mul_decompose_gathered(gathered, other_local.nrow, self.full_moduli, self.grid.tpg, small=small)
+        the limb axis (started here, or earlier by gather_towers_async and passed as `gathered`), then digits + NTT + MAC
+        on the local limbs (lhs: all columns of S on this rank's limbs)"""
+        handle = gathered if gathered is not None else self.gather_towers_async(other_local)
+        g = self.wait_towers(handle)
+        return lhs_local_limbs.mul_decompose_gathered(g, handle[2], self.full_moduli, self.grid.tpg, small=small)
 
     # -- the column-axis exchange ---------------------------------------------------------------------------------------
     def all_gather_columns(self, local: GpuDCRTPolyMatrix, ncol: int) -> GpuDCRTPolyMatrix:

@@ -566,6 +566,11 @@ class GpuDCRTPolyMatrix:
                      "gpu_matrix_mul_decompose_gathered", self._L)
         return out
 
+    def intt_rows_from(self, src, dst_row: int = 0):
+        """rows [dst_row, dst_row + src.nrow) of self <- coefficient form of src, src untouched (extension gpu_matrix_intt_to)"""
+        check_status(self._L.gpu_matrix_intt_to(self.raw, dst_row, src.raw), "gpu_matrix_intt_to", self._L)
+        self.is_ntt = False
+
     def add_scaled_block_from(self, src, scalar, dst_row, dst_col, src_row, src_col, rows, cols):
         """self[block] += src[block] * scalar (scalar 1x1; all EVAL) in one launch (extension gpu_matrix_add_scaled_block)"""
         check_status(self._L.gpu_matrix_add_scaled_block(self.raw, src.raw, scalar.raw, dst_row, dst_col, src_row, src_col, rows, cols),

@@ -17,6 +17,9 @@ sys.path.insert(0, ROOT)
 
 
 def main():
+    import faulthandler
+
+    faulthandler.enable()
     import torch
     import torch.distributed as dist
 
@@ -83,8 +86,10 @@ def main():
         left = StackedEncoding(sl(np.concatenate([enc["lv"], enc["lp"]], axis=0), False), 1, sl(enc["lx"], False))
         rv, rp, rx = sl(enc["rv"], True), sl(enc["rp"], True), sl(enc["rx"], False)
         ev = GridBggEvaluator(g)
-        for _ in range(2):
-            left = ev.mul_gate_stacked(left, rv, rp, rx, m)
+        handle = ev.prefetch(rp)  # the second gate's exchange is started before the first gate's product
+        nxt = ev.prefetch(rp)
+        left = ev.mul_gate_stacked(left, rv, rp, rx, m, gathered=handle)
+        left = ev.mul_gate_stacked(left, rv, rp, rx, m, gathered=nxt)
         st = left.stacked.to_rns()
         check(f"grid {lg}x{cg} chain", np.array_equal(st[:1], chain_vec[:, :, t0:t1]) and np.array_equal(st[1:], chain_pk[:, :, t0:t1])
               and np.array_equal(left.plaintext.to_rns(), chain_pt[:, :, t0:t1]))
