@@ -156,6 +156,10 @@ int gpu_matrix_load_bigint_batch(GpuMatrix *mat, const uint64_t *words, size_t w
 int gpu_matrix_store_bigint_batch(const GpuMatrix *mat, uint64_t *words_out, size_t words_per_coeff, GpuEventSet **out_events);
 /* The CUDA stream (cudaStream_t) all work of this context is ordered on; for CUDA-event timing. */
 void *gpu_context_stream(const GpuContext *ctx);
+/* Stream override for the CALLING THREAD: this library's launches go to `stream` (a cudaStream_t) instead of each context's
+ * stream until it is called with NULL.  Ordering against the context stream is the caller's business (events); allocation
+ * stays on the context stream, so only operations on existing buffers belong on a side stream. */
+int gpu_thread_stream_override(void *stream);
 /* Device pointer / word size (4 or 8) / format of a matrix's storage, [poly][limb][coeff]. */
 int gpu_matrix_device_info(const GpuMatrix *mat, void **out_ptr, int *out_word_bytes, int *out_format);
 /* Number of kernels launched by this library since process start (bench.py's gpu_launches). */

@@ -135,7 +135,7 @@ class GridBggEvaluator:
         self.ops = ops
 
     def prefetch(self, right_pk_local: GpuDCRTPolyMatrix):
-        return self.ops.gather_towers_async(right_pk_local)
+        return self.ops.gather_towers_async(right_pk_local, side_stream=True)
 
     def mul_gate_stacked(self, left: StackedEncoding, right_vec_local: GpuDCRTPolyMatrix, right_pk_local: GpuDCRTPolyMatrix,
                          right_plaintext: GpuDCRTPolyMatrix | None, ncol: int, gathered=None) -> StackedEncoding:

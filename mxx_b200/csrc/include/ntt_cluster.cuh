@@ -203,32 +203,52 @@ GP_HD void cl_fwd_push(const Src &src, const Peers &peers, uint32_t rank, const 
     constexpr int C = 1 << LC, V = ClVec<T>::kVec;
     constexpr uint32_t B = 1u << LOGB, per = B >> LC, vecs = per / V;
     // every thread runs the same number of iterations (the aligned cluster barrier below sits inside the loop)
-    static_assert(vecs % FastCfg<T, LOGB>::kThreads == 0, "push plan: whole iterations for every thread");
+    constexpr uint32_t NT = FastCfg<T, LOGB>::kThreads;
+    static_assert(vecs % NT == 0, "push plan: whole iterations for every thread");
+    // U iterations are batched: all their global loads (U*C 128-bit loads per thread) are issued before the first
+    // butterfly.  ncu put 20 % of the u32 2^15 kernel's stall samples on the first butterfly after a 2-load iteration
+    // (profiles/r02_ncu_cluster_summary.txt), but batching 2 / 4 / 8 / 16 loads measured the same within 1 % (16: slower,
+    // registers) — the other two resident CTAs already fill those slots (profiles/r02_push_sweep.txt)
+#ifndef GP_PUSH_LOADS
+#define GP_PUSH_LOADS 4
+#endif
+    constexpr uint32_t iters = vecs / NT;
+    constexpr uint32_t U = (GP_PUSH_LOADS / C) < 1 ? 1u : ((GP_PUSH_LOADS / C) > iters ? iters : (uint32_t)(GP_PUSH_LOADS / C));
+    static_assert(iters % U == 0, "push plan: whole batches");
     bool first = true;
 #pragma unroll 1
-    for (uint32_t v = GP_TID; v < vecs; v += GP_NT) {
-        const uint32_t e = rank * per + V * v;
-        T x[V][C];
+    for (uint32_t v0 = GP_TID; v0 < vecs; v0 += U * GP_NT) {
+        T x[U][V][C];
 #pragma unroll
-        for (int j = 0; j < C; j++) {
-            T t[V];
-            src_ldv(src, e + (uint32_t)j * B, t);
+        for (uint32_t u = 0; u < U; u++) {
+            const uint32_t e = rank * per + V * (v0 + u * GP_NT);
 #pragma unroll
-            for (int k = 0; k < V; k++) x[k][j] = t[k];
+            for (int j = 0; j < C; j++) {
+                T t[V];
+                src_ldv(src, e + (uint32_t)j * B, t);
+#pragma unroll
+                for (int k = 0; k < V; k++) x[u][k][j] = t[k];
+            }
         }
 #pragma unroll
-        for (int k = 0; k < V; k++) fwd_net<T, LC, NOCSUB>(x[k], tw, 1u, q, q2);
+        for (uint32_t u = 0; u < U; u++) {
+#pragma unroll
+            for (int k = 0; k < V; k++) fwd_net<T, LC, NOCSUB>(x[u][k], tw, 1u, q, q2);
+        }
         if (first) {
             cl_wait();
             first = false;
         }
-        const uint32_t at = padw(e);
 #pragma unroll
-        for (int j = 0; j < C; j++) {
-            T t[V];
+        for (uint32_t u = 0; u < U; u++) {
+            const uint32_t at = padw(rank * per + V * (v0 + u * GP_NT));
 #pragma unroll
-            for (int k = 0; k < V; k++) t[k] = x[k][j];
-            peers.stv(j, at, t);
+            for (int j = 0; j < C; j++) {
+                T t[V];
+#pragma unroll
+                for (int k = 0; k < V; k++) t[k] = x[u][k][j];
+                peers.stv(j, at, t);
+            }
         }
     }
 }

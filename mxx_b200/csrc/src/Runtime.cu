@@ -205,6 +205,15 @@ int gpu_context_get_N(const GpuContext *ctx, int *out_N) {
 
 void *gpu_context_stream(const GpuContext *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
 
+// extension: the CUDA stream the CALLING THREAD's kernel launches of this library go to (nullptr: back to each context's own
+// stream).  Lets a caller run an operation on a side stream of its own — the operand exchange of a limb-sharded gate one
+// gate ahead of the product (mxx_b200/dist.py) — with the ordering against the context stream done by the caller's events.
+// Matrices are still allocated on the context stream: only operations on buffers that already exist belong on a side stream.
+int gpu_thread_stream_override(void *stream) {
+    gp::tl_stream = (cudaStream_t)stream;
+    return 0;
+}
+
 int gpu_event_set_wait(GpuEventSet *events) {
     if (!events) return gp::set_error("invalid gpu_event_set_wait arguments");
     if (events->event) {

@@ -309,31 +309,73 @@ class GridShardedOps:
         return ColumnShards(ncol, self.grid.col_groups)
 
     # -- the limb-axis exchange: coefficient form of the right operand, all towers ---------------------------------
-    def gather_towers_async(self, other_local: GpuDCRTPolyMatrix):
+    def gather_towers_async(self, other_local: GpuDCRTPolyMatrix, side_stream: bool = False):
         """Starts the exchange and returns a handle for `mul_decompose(..., gathered=handle)`.
 
         (d x c) on this rank's towers, EVAL or COEFF -> (limb_groups*d x c) COEFF matrix of this rank's context whose rows
         [g*d, (g+1)*d) hold limb group g's towers (the layout gpu_matrix_mul_decompose_gathered reads).  The inverse
         transform writes this rank's block in place and the all-gather is an IN-PLACE ncclAllGather on that buffer, issued
         asynchronously: it runs on NCCL's stream while the context stream goes on with whatever is enqueued next (the
-        product of the PREVIOUS gate when an evaluator prefetches its right operands); `wait_towers` joins it."""
+        product of the PREVIOUS gate when an evaluator prefetches its right operands); `wait_towers` joins it.
+
+        side_stream=True (prefetching evaluators): the inverse transform too leaves the context stream.  It runs on this
+        object's exchange stream, into one of two persistent buffers, after an event that marks "everything enqueued on the
+        context stream so far" — which covers the producer of `other_local` and the product that last read the buffer —
+        so neither the transform nor the all-gather is on the critical path of the product enqueued next."""
         torch, dist = _torch()
         d = other_local.nrow
-        out = GpuDCRTPolyMatrix(self.params, self.grid.limb_groups * d, other_local.ncol, level=other_local.level, is_ntt=False)
-        out.intt_rows_from(other_local, self.a * d)
-        work = None
-        if self.grid.limb_groups > 1:
-            buf = device_tensor(out)
-            per = buf.numel() // self.grid.limb_groups
-            with self._stream():
+        groups = self.grid.limb_groups
+        if not side_stream:
+            out = GpuDCRTPolyMatrix(self.params, groups * d, other_local.ncol, level=other_local.level, is_ntt=False)
+            out.intt_rows_from(other_local, self.a * d)
+            work = None
+            if groups > 1:
+                buf = device_tensor(out)
+                per = buf.numel() // groups
+                with self._stream():
+                    work = dist.all_gather_into_tensor(buf, buf[self.a * per:(self.a + 1) * per], group=self.limb_group, async_op=True)
+            return (out, work, d, None)
+        key = (groups * d, other_local.ncol, other_local.level)
+        if getattr(self, "_xkey", None) != key:  # (re)create the two persistent exchange buffers and their tensor views
+            self._xkey = key
+            self._xbuf = [GpuDCRTPolyMatrix(self.params, key[0], key[1], level=key[2], is_ntt=False) for _ in range(2)]
+            self._xten = [device_tensor(m) for m in self._xbuf]
+            self._xi, self._xpending = 0, 0
+            if getattr(self, "_x", None) is None:
+                self._x = torch.cuda.Stream(device=f"cuda:{self.params.gpu_ids[0]}")
+        if getattr(self, "_xpending", 0) >= 2:
+            raise RuntimeError("at most two side-stream exchanges may be in flight (two persistent buffers)")
+        self._xpending = getattr(self, "_xpending", 0) + 1
+        i = self._xi
+        self._xi ^= 1
+        out, buf = self._xbuf[i], self._xten[i]
+        L = self.params._L
+        with self._stream():
+            ev = torch.cuda.current_stream().record_event()  # everything enqueued on the context stream so far
+        self._x.wait_event(ev)
+        L.gpu_thread_stream_override(self._x.cuda_stream)
+        try:
+            out.intt_rows_from(other_local, self.a * d)
+        finally:
+            L.gpu_thread_stream_override(None)
+        work, done = None, None
+        if groups > 1:
+            per = buf.numel() // groups
+            with torch.cuda.stream(self._x):
                 work = dist.all_gather_into_tensor(buf, buf[self.a * per:(self.a + 1) * per], group=self.limb_group, async_op=True)
-        return (out, work, d)
+        else:
+            done = self._x.record_event()
+        return (out, work, d, done)
 
     def wait_towers(self, handle) -> GpuDCRTPolyMatrix:
-        out, work, _ = handle
-        if work is not None:
-            with self._stream():
+        out, work, _, done = handle
+        if any(out is m for m in getattr(self, "_xbuf", ())):
+            self._xpending = max(0, self._xpending - 1)
+        with self._stream():
+            if work is not None:
                 work.wait()  # the context stream waits for NCCL's stream; the host does not block
+            if done is not None:
+                _torch()[0].cuda.current_stream().wait_event(done)
         return out
 
     def gather_towers(self, other_local: GpuDCRTPolyMatrix) -> GpuDCRTPolyMatrix:

@@ -82,6 +82,7 @@ EXTENSIONS = {
     "gpu_matrix_load_bigint_batch": (C.c_int, [H, u64p, C.c_size_t, C.c_int, vpp]),
     "gpu_matrix_store_bigint_batch": (C.c_int, [H, u64p, C.c_size_t, vpp]),
     "gpu_context_stream": (C.c_void_p, [H]),
+    "gpu_thread_stream_override": (C.c_int, [C.c_void_p]),
     "gpu_matrix_device_info": (C.c_int, [H, vpp, intp, intp]),
     "gpu_kernel_launch_count": (C.c_uint64, []),
     "gpu_timer_create": (C.c_int, [H, vpp]),

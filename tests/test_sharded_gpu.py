@@ -142,3 +142,70 @@ def test_stacked_gate_equals_reference_sequence(mx):
     ev = ShardedBggEvaluator(ColumnShardedOps(params))  # one rank: the whole matrix is the local block
     got = ev.mul_gate_stacked(StackedEncoding.from_encoding(left), right.vector, right.pubkey.matrix, right.plaintext, m).to_encoding()
     assert got.vector == want.vector and got.pubkey.matrix == want.pubkey.matrix and got.plaintext == want.plaintext
+
+
+@pytest.mark.parametrize("n,depth,bits", [(1 << 12, 3, 24), (1 << 15, 2, 28), (1 << 14, 2, 51)])
+def test_intt_to_block_and_side_stream(mx, n, depth, bits):
+    """gpu_matrix_intt_to: rows of a larger buffer <- coefficient form of src (src untouched), on the context stream and
+    on a caller's side stream (gpu_thread_stream_override)"""
+    import torch
+
+    moduli = mx.standard_moduli(n, depth, bits)
+    params, plan = mx.GpuDCRTPolyParams(n, moduli, 12), orc.Plan(n, moduli)
+    ev = plan.uniform(2, 3, seed=5)
+    src = mx.GpuDCRTPolyMatrix.from_rns(params, ev, True)
+    buf = mx.GpuDCRTPolyMatrix.from_rns(params, np.zeros((6, 3, depth, n), dtype=np.uint64), False)
+    buf.intt_rows_from(src, 2)
+    want = np.zeros((6, 3, depth, n), dtype=np.uint64)
+    want[2:4] = plan.intt(ev)
+    assert np.array_equal(buf.to_rns(), want) and np.array_equal(src.to_rns(), ev)
+    # the same on a side stream ordered by the caller's events
+    side = torch.cuda.Stream()
+    params.synchronize()
+    L = params._L
+    L.gpu_thread_stream_override(side.cuda_stream)
+    try:
+        buf.intt_rows_from(src, 4)
+    finally:
+        L.gpu_thread_stream_override(None)
+    side.synchronize()
+    want[4:6] = plan.intt(ev)
+    assert np.array_equal(buf.to_rns(), want)
+    coeff = mx.GpuDCRTPolyMatrix.from_rns(params, want[2:4], False)  # a COEFF source is copied
+    buf.intt_rows_from(coeff, 0)
+    want[0:2] = want[2:4]
+    assert np.array_equal(buf.to_rns(), want)
+    with pytest.raises(mx.ffi.GpuError):
+        buf.intt_rows_from(src, 5)  # does not fit
+
+
+def test_chunked_load_with_more_workers_than_ring_slots():
+    """The chunked host->device load with its worker threads outnumbering the pinned ring slots, many loads in a row, in a
+    fresh process (the worker count is fixed at first use).  Regression test for a worker that notified the caller's
+    condition variable after the caller could leave (seen as memory corruption with 8 ranks x 31 workers on 24 slots)."""
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = r'''
+import sys, numpy as np
+sys.path.insert(0, %r)
+import mxx_b200 as mx
+n, depth = 1 << 14, 8
+moduli = mx.standard_moduli(n, depth, 24)
+params = mx.GpuDCRTPolyParams(n, moduli, 12)
+rng = np.random.default_rng(1)
+host = rng.integers(0, min(moduli), size=(1, 160, depth, n), dtype=np.uint64)   # 21 M words: the chunked path
+pin = mx.PinnedBuffer(host.shape)
+pin.array[...] = host
+g = mx.GpuDCRTPolyMatrix(params, 1, 160)
+for i in range(40):
+    g.load_rns(pin.array if i %% 2 else host, mx.GPU_POLY_FORMAT_EVAL, wait=True)
+    (g + g).to_rns() if i %% 8 == 0 else None
+assert np.array_equal(g.to_rns(), host)
+print("loads ok")
+''' % root
+    env = dict(os.environ, MXX_LOAD_THREADS="24", MXX_LOAD_SLOTS="3", MXX_LOAD_CHUNK_LOG="18")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0 and "loads ok" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
