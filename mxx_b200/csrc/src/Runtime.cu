@@ -163,6 +163,7 @@ int gpu_context_create(uint32_t logN, uint32_t L, uint32_t dnum, const uint64_t 
         ctx->f64_mac_fold = f64_mac_fold_terms(qmax);
         if (const char *env = getenv("MXX_MATMUL_F64")) ctx->f64_matmul = env[0] != '0';
         ctx->nocsub = nocsub_ok(qmax, ctx->wide);
+        if (const char *env = getenv("MXX_NTT_NOCSUB")) ctx->nocsub = ctx->nocsub && env[0] != '0';  // A/B: keep the conditional subtractions
         if (const char *env = getenv("MXX_NTT_GENERIC")) ctx->force_generic_ntt = env[0] == '1';
         if (const char *env = getenv("MXX_DECOMP_FUSE_TOP")) ctx->fuse_decompose_top = env[0] != '0';
         if (const char *env = getenv("MXX_NTT_BLOCK_LOG")) ctx->ntt_block_override = atoi(env);

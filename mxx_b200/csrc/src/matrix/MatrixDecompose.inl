@@ -252,6 +252,7 @@ extern "C" int gpu_matrix_fill_small_decomposed_identity_chunk(GpuMatrix *out, c
 // output columns (MXX_MUL_DECOMPOSE_SCRATCH_BYTES bounds the digit scratch; the reference's
 // knob is MXX_MUL_DECOMPOSE_COLUMN_CHUNK_WIDTH, src/env.rs:148).
 namespace {
+constexpr size_t kOneChunkMinCtas = 8192;  // digit-NTT CTAs (64 KB blocks) from which the product runs as ONE chunk
 // out = lhs * G^-1(source columns [col0, col0 + out->cols)): per column chunk one fused digit+NTT kernel and one product
 // kernel writing straight into the output columns.  `coeff` is the coefficient-form source: an ordinary d x c matrix of
 // this context, or (gs != nullptr) the gathered blocks of a limb-sharded operand.
@@ -276,9 +277,16 @@ int mul_decompose_core(GpuContext *ctx, GpuMatrix *out, const GpuMatrix *lhs, co
     // the last, partial wave cheap (C3-a: 450 CTAs per column on 444 resident slots).  Two chunks run
     // concurrently on the two auxiliary streams, so one chunk's product overlaps the other's NTTs.
     size_t width = std::max<size_t>(1, (budget / 2) / std::max<size_t>(1, m * poly_bytes));
-    width = std::min(width, oc >= 2 ? (oc + 1) / 2 : oc);
+    // One chunk or two lanes?  Measured on B200 (tools/md_lanes_ab.py, profiles/r02_md_lanes_ab.txt): launches of many waves are
+    // 6-8 % faster as ONE chunk on the context stream (C3-a 0.90 -> 0.83 ms, C3-b 20.3 -> 19.1 ms: no product kernel competing
+    // with the digit-NTT kernel, fewer partial waves), small ones 2-7 % faster as two chunks on the auxiliary streams (the second
+    // chunk's CTAs fill the first one's tail; a limb-sharded C4 gate on 8 GPUs is 2300 CTAs).  MXX_MUL_DECOMPOSE_LANES=1|2 forces either.
+    static const int lanes_knob = getenv("MXX_MUL_DECOMPOSE_LANES") ? atoi(getenv("MXX_MUL_DECOMPOSE_LANES")) : 0;
+    const size_t ctas_all = ((m * oc * limbs) << ctx->logN) >> (sizeof(T) == 4 ? 14 : 13);
+    const bool one_lane = lanes_knob == 1 || (lanes_knob == 0 && ctas_all >= kOneChunkMinCtas);
+    width = std::min(width * (one_lane ? 2 : 1), one_lane ? oc : (oc >= 2 ? (oc + 1) / 2 : oc));
     const size_t chunks = (oc + width - 1) / width;
-    const int lanes = chunks > 1 ? 2 : 1;
+    const int lanes = chunks > 1 ? 2 : 1;  // a job too large for one chunk of the scratch budget alternates wide chunks over the two lanes
     Scratch digits[2];
     for (int i = 0; i < lanes; i++)
         if (digits[i].alloc(m * width * poly_bytes, ctx->stream)) return 1;
