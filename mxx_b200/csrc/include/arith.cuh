@@ -275,11 +275,16 @@ GP_HD void matmul_thread(uint32_t bx, uint32_t by, uint32_t bz, uint32_t tid, ui
 // UNROLL (inner-dimension unroll) and NT (CTA size) are tuned per tile shape on the C1-R product
 // (tools/matmul_lab.cu): <1,6> unroll 2 / 64 threads and <1,1> unroll 6 / 128 threads stream the right
 // operand at the measured HBM copy bandwidth; see DESIGN.md 4.
-template <typename T, int V, int TR, int TC, int UNROLL = 2, int NT = 128>
+// COLS_FAST: the column tiles are the fastest-varying CTA index (grid x = column tiles, y = limb x slot chunk), so the
+// CTAs resident at one time share a few (limb, slot chunk) slices of A and every A word is fetched from HBM once.
+// With the slot chunks fastest, one sweep over x touches ALL of A before any of it is used again: a left operand
+// larger than the L2 (C3-b: 4 x 120 polynomials = 472 MB) is streamed once per column tile.
+template <typename T, int V, int TR, int TC, int UNROLL = 2, int NT = 128, bool COLS_FAST = false>
 __global__ void __launch_bounds__(NT)
 matmul_kernel(T *__restrict__ out, const T *__restrict__ A, const T *__restrict__ B, MatmulGeom g,
               const LimbConst<T> *__restrict__ lc) {
-    matmul_thread<T, V, TR, TC, UNROLL>(blockIdx.x, blockIdx.y, blockIdx.z, threadIdx.x, blockDim.x, out, A, B, g, lc);
+    matmul_thread<T, V, TR, TC, UNROLL>(COLS_FAST ? blockIdx.y : blockIdx.x, COLS_FAST ? blockIdx.x : blockIdx.y, blockIdx.z,
+                                        threadIdx.x, blockDim.x, out, A, B, g, lc);
 }
 
 // ---- the same product on the FP64 pipe (u64 words, every modulus below 2^51; modarith.cuh f64_*) --------------
@@ -369,11 +374,12 @@ GP_HD void matmul_f64_thread(uint32_t bx, uint32_t by, uint32_t bz, uint32_t tid
         }
 }
 // MINB caps the registers (ptxas took 222 for the 2 x 4 tile uncapped: 8 warps per SM, 3.7 TB/s)
-template <int V, int TR, int TC, int UNROLL = 2, int NT = 128, int MINB = 512 / NT>
+template <int V, int TR, int TC, int UNROLL = 2, int NT = 128, bool COLS_FAST = false, int MINB = 512 / NT>
 __global__ void __launch_bounds__(NT, MINB)
 matmul_f64_kernel(uint64_t *__restrict__ out, const uint64_t *__restrict__ A, const uint64_t *__restrict__ B, MatmulGeom g,
                   const LimbConst<F64> *__restrict__ lc) {
-    matmul_f64_thread<V, TR, TC, UNROLL>(blockIdx.x, blockIdx.y, blockIdx.z, threadIdx.x, blockDim.x, out, A, B, g, lc);
+    matmul_f64_thread<V, TR, TC, UNROLL>(COLS_FAST ? blockIdx.y : blockIdx.x, COLS_FAST ? blockIdx.x : blockIdx.y, blockIdx.z,
+                                         threadIdx.x, blockDim.x, out, A, B, g, lc);
 }
 
 }  // namespace gp

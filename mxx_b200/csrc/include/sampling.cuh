@@ -118,6 +118,8 @@ struct ChaChaStream {
         pos++;
         return v;
     }
+    // stream words handed out so far by a stream opened at block counter stream0 (fewer than 2^35)
+    GP_HD uint32_t consumed(uint64_t stream0) const { return pos == 8 && ctr[0] == (uint32_t)stream0 ? 0u : (ctr[0] - (uint32_t)stream0 - 1u) * 8u + pos; }
     // uniform deviate in the open interval (0,1), 53 bits
     static GP_HD double to_unit(uint64_t w) {
         const double scale = 1.0 / 9007199254740992.0;
@@ -173,7 +175,7 @@ struct KarneyMachine {
     enum : uint32_t { kGH0, kGH1, kGH2, kPH0, kPH1, kPH2, kSign, kJ, kB0, kB1, kFb1, kFb2, kDone };
     uint32_t st;
     int32_t k, n, h, bn, tries;
-    double mean, sd, hv, x, x0, y, z;
+    double mean, sd, hv, x, x0, y, z, bthr;  // bthr = (2k + x) / (2k + 2), fixed for all B tests of one attempt
     int64_t i0, j, sgn, span, result;
 
     GP_HD bool done() const { return st == kDone; }
@@ -229,7 +231,7 @@ struct KarneyMachine {
         if (st == kB0 || st == kB1) {
             // B: z = U, !(z < y) ends; r = U, !(r < (2k + x) / (2k + 2)) ends; y = z; ...
             const bool first = st == kB0;
-            const double thr = first ? y : (2.0 * (double)k + x) / (double)(2 * k + 2);
+            const double thr = first ? y : bthr;
             if (first) z = u;
             if (!(u < thr)) b_result();
             else if (first) st = kB1;
@@ -253,7 +255,7 @@ struct KarneyMachine {
                 j = (int64_t)(w % (uint64_t)span);
                 x = x0 + (double)j / sd;
                 if (!(x < 1.0) || (x == 0.0 && sgn < 0 && k == 0)) restart();
-                else h = k + 1, b_check();
+                else h = k + 1, bthr = (2.0 * (double)k + x) / (double)(2 * k + 2), b_check();
                 break;
             case kFb1:
                 hv = u, st = kFb2;
@@ -270,9 +272,14 @@ struct KarneyMachine {
     }
 };
 
-// integer z ~ D_{Z, stddev, mean}.  (Consecutive draws of one stream are separate calls: the lanes of a warp meet again
-// between them.  A variant that chained the draws through a task object holding pointers to the caller's local arrays
-// faulted on the device with nvcc 12.9 although the same code is correct on the host — tools/sampler_lab.cu.)
+// integer z ~ D_{Z, stddev, mean}: ONE draw from a stream.  Callers that draw several integers from the same stream
+// (gq_sample_digits, p1_sample_column) do not call this once per integer: after the first draw the lanes of a warp
+// would sit at different positions of their key-stream blocks, and from then on every step of the following draws
+// would find 1/8 of the lanes at a block boundary — a ~1000-instruction ChaCha permutation executed per STEP with
+// 4 of 32 lanes active (ncu on the round-1 kernel: 67 % of the warp instructions with 4-7 lanes,
+// profiles/r01_ncu_sampler.txt).  They run one loop over the whole task instead, in which every lane takes exactly
+// one word per trip and a finished draw hands over to the next one inside the trip: positions stay equal across
+// the warp and all lanes refill together.  The word sequence each draw sees is unchanged.
 GP_HD int64_t karney_integer(ChaChaStream &g, double mean, double stddev) {
     KarneyMachine km;
     km.begin(mean, stddev);
@@ -308,61 +315,218 @@ GP_HD uint64_t draw_uniform_residue(const Seed256 &seed, uint64_t global_poly, u
 // ---- G-lattice sampler, one (poly, coeff, tower) --------------------------------------
 // Writes the dpt signed digits x with  sum_i x_i b^i == value (mod q)  and x ~ D_{Lambda, c}.
 // DMAX bounds the local arrays (8 covers every base >= ceil(crt_bits/8); 64 is the ABI limit).
-template <int DMAX>
-GP_HD void gq_sample_digits(const Seed256 &seed, uint64_t value, uint64_t q, uint32_t base_bits, uint32_t dpt, double c,
-                            uint32_t tower, uint64_t poly, uint64_t coeff, int64_t *digits_out) {
-    const uint64_t base = 1ULL << base_bits;
-    const double bf = (double)base;
-    const double sigma = c / (bf + 1.0);
-    const double kf = (double)dpt;
-    const uint32_t last = dpt - 1;
-
-    int64_t qd[DMAX], vd[DMAX], z[DMAX];
-    double cv[DMAX], a[DMAX], zf[DMAX];
-    {
-        uint64_t qq = q, vv = value;
+// The three pieces below are shared by the one-task form (gq_sample_digits) and the lane-balanced form
+// (gq_sample_digits_batch), so both evaluate the same floating-point expressions.
+template <int DMAX> struct GqTower {  // what depends on (q, base, dpt, c) only
+    uint32_t base_bits, dpt, last;
+    uint64_t base;
+    double bf, sigma, kf;
+    int64_t qd[DMAX];
+    double cv[DMAX];
+    GP_HD void init(uint64_t q, uint32_t base_bits_, uint32_t dpt_, double c) {
+        base_bits = base_bits_, dpt = dpt_, last = dpt_ - 1;
+        base = 1ULL << base_bits;
+        bf = (double)base;
+        sigma = c / (bf + 1.0);
+        kf = (double)dpt;
+        uint64_t qq = q;
         for (uint32_t i = 0; i < dpt; i++) {
             qd[i] = (int64_t)(qq & (base - 1));
-            vd[i] = (int64_t)(vv & (base - 1));
             qq >>= base_bits;
-            vv >>= base_bits;
+        }
+        cv[0] = (double)qd[0] / bf;
+        for (uint32_t i = 1; i < dpt; i++) cv[i] = (cv[i - 1] + (double)qd[i]) / bf;
+    }
+    GP_HD int64_t value_digit(uint64_t value, uint32_t i) const { return (int64_t)((value >> (base_bits * i)) & (base - 1)); }
+    // the running target a[] of one task: dpt continuous normals (the first 2 dpt words of the stream), the perturbation
+    // p = L-factor of the covariance times zf, folded in
+    GP_HD void target(ChaChaStream &g, uint64_t value, double *a) const {
+        double zf[DMAX];
+        for (uint32_t i = 0; i < dpt; i++) zf[i] = sigma * g.normal();
+        double prev = 0.0;
+        for (uint32_t t = 0; t < dpt; t++) {
+            const double lt = t == 0 ? sqrt(bf * (1.0 + 1.0 / kf) + 1.0) : sqrt(bf * (1.0 + 1.0 / (kf - (double)t)));
+            double p;
+            if (t < last) {
+                const double hn = sqrt(bf * (1.0 - 1.0 / (kf - (double)t)));  // h[t+1]
+                p = lt * zf[t] + hn * zf[t + 1];
+            } else {
+                const double hl = t == 0 ? 0.0 : sqrt(bf * (1.0 - 1.0 / (kf - (double)(t - 1))));  // h[last]
+                p = hl * zf[t];
+            }
+            const double vdt = (double)value_digit(value, t);
+            a[t] = t == 0 ? (vdt - p) / bf : (prev + vdt - p) / bf;
+            prev = a[t];
         }
     }
-    cv[0] = (double)qd[0] / bf;
-    for (uint32_t i = 1; i < dpt; i++) cv[i] = (cv[i - 1] + (double)qd[i]) / bf;
+    // a finished draw of the chain z[last], z[0], .., z[last-1] (`drawn` = draws finished before this one); returns false
+    // when it was the last one, otherwise the (mean, deviation) of the next draw
+    GP_HD bool chain(uint32_t drawn, int64_t r, double *a, int64_t *z, double &mean, double &sd) const {
+        if (drawn == 0) {
+            z[last] = r;
+            for (uint32_t i = 0; i < dpt; i++) a[i] += (double)r * cv[i];
+        } else {
+            z[drawn - 1] = r;
+        }
+        if (drawn == last) return false;
+        mean = -a[drawn], sd = sigma;
+        return true;
+    }
+    GP_HD void digits(uint64_t value, const int64_t *z, int64_t *out) const {
+        const int64_t sb = (int64_t)base;
+        if (dpt == 1) {
+            out[0] = sb * z[0] + qd[0] * z[0] + value_digit(value, 0);
+            return;
+        }
+        out[0] = sb * z[0] + qd[0] * z[last] + value_digit(value, 0);
+        for (uint32_t i = 1; i < last; i++) out[i] = sb * z[i] - z[i - 1] + qd[i] * z[last] + value_digit(value, i);
+        out[last] = qd[last] * z[last] - z[last - 1] + value_digit(value, last);
+    }
+};
 
+template <int DMAX>
+GP_HD void gq_sample_digits(const Seed256 &seed, uint64_t value, uint64_t q, uint32_t base_bits, uint32_t dpt, double c,
+                            uint32_t tower, uint64_t poly, uint64_t coeff, int64_t *digits_out, uint32_t *words_used = nullptr) {
+    GqTower<DMAX> tw;
+    tw.init(q, base_bits, dpt, c);
+    int64_t z[DMAX];
+    double a[DMAX];
     ChaChaStream g;
     g.open(seed, (uint64_t)tower + 1, poly + 1, coeff + 1, kDomGadget);
-    for (uint32_t i = 0; i < dpt; i++) zf[i] = sigma * g.normal();
-
-    // perturbation p = L-factor of the covariance times zf, folded into the running target a
-    double prev = 0.0;
-    for (uint32_t t = 0; t < dpt; t++) {
-        const double lt = t == 0 ? sqrt(bf * (1.0 + 1.0 / kf) + 1.0) : sqrt(bf * (1.0 + 1.0 / (kf - (double)t)));
-        double p;
-        if (t < last) {
-            const double hn = sqrt(bf * (1.0 - 1.0 / (kf - (double)t)));  // h[t+1]
-            p = lt * zf[t] + hn * zf[t + 1];
-        } else {
-            const double hl = t == 0 ? 0.0 : sqrt(bf * (1.0 - 1.0 / (kf - (double)(t - 1))));  // h[last]
-            p = hl * zf[t];
+    tw.target(g, value, a);
+    // z[last] ~ D(-a[last]/cv[last], sigma/cv[last]), then a += z[last] cv and z[i] ~ D(-a[i], sigma) for i < last —
+    // as one word-per-trip loop (see karney_integer)
+    {
+        KarneyMachine km;
+        uint32_t drawn = 0;
+        km.begin(-a[tw.last] / tw.cv[tw.last], tw.sigma / tw.cv[tw.last]);
+        for (;;) {
+            bool fin = false;
+            while (km.done()) {  // also a draw that needs no word at all (degenerate deviation)
+                double mean, sd;
+                if (!tw.chain(drawn, km.result, a, z, mean, sd)) {
+                    fin = true;
+                    break;
+                }
+                km.begin(mean, sd);
+                ++drawn;
+            }
+            if (fin) break;
+            km.step(g.next());
         }
-        a[t] = t == 0 ? ((double)vd[0] - p) / bf : (prev + (double)vd[t] - p) / bf;
-        prev = a[t];
     }
+    if (words_used) *words_used = g.consumed((uint64_t)tower + 1);  // host-side lane-utilisation model only (src/emu.cu)
+    tw.digits(value, z, digits_out);
+}
 
-    z[last] = karney_integer(g, -a[last] / cv[last], sigma / cv[last]);
-    for (uint32_t i = 0; i < dpt; i++) a[i] += (double)z[last] * cv[i];
-    for (uint32_t i = 0; i < last; i++) z[i] = karney_integer(g, -a[i], sigma);
-
-    const int64_t sb = (int64_t)base;
-    if (dpt == 1) {
-        digits_out[0] = sb * z[0] + qd[0] * z[0] + vd[0];
-        return;
+// ---- lane-balanced form: a thread runs K tasks through ONE word-per-trip loop --------------------------------------------
+// The number of words a draw consumes is long-tailed (G-lattice task with two digits: mean 42, 99th percentile 124), so a
+// warp whose lanes own one task each runs for the longest of 32 tasks: 12 of 32 lanes busy on average (warp model over
+// the word counts of real streams, tests/test_samplers.py).  Here a lane owns K tasks and moves to its next one as soon
+// as the current one is done, so the warp runs for the longest SUM of K: 18 of 32 lanes busy for K = 4, 21 for K = 8.
+// What keeps this in lock step:
+//   * everything that is not the rejection loop runs for all K tasks up front (HChaCha20 key derivation; for the G-lattice
+//     sampler also the continuous normals — log, cos, sqrt — and the target a[]) or at the end (digits, RNS reduction,
+//     stores), with all lanes active;
+//   * a lane takes its next task only on a trip at which the whole warp is at a key-stream block boundary, and first skips
+//     the words the up-front phase has already used, so the position inside the block stays equal across the warp
+//     and all lanes run the ChaCha permutation together (cost: 3.5 idle trips per task on average).
+// Each task reads exactly the words the one-task form reads, so the samples are identical.
+struct BatchLane {
+    ChaChaStream g;
+    KarneyMachine km;
+    uint32_t cur, skip, drawn;  // task index; words still to skip; finished draws of the current task
+    bool active;                // inside a task (false: waiting for a block boundary, or out of tasks)
+    GP_HD void start() { cur = 0, skip = 0, drawn = 0, active = false, g.pos = 8; }
+    GP_HD bool at_boundary() const { return g.pos >= 8; }
+    // point the stream at word `used` of the stream (key, stream0, stream1); only on a block-boundary trip, so that the
+    // refill inside the next g.next() produces the block that word lives in
+    GP_HD void resume(const uint32_t *key, uint64_t stream0, uint64_t stream1, uint32_t used) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) g.key[i] = key[i];
+        const uint64_t blk = stream0 + (used >> 3);
+        g.ctr[0] = (uint32_t)blk, g.ctr[1] = (uint32_t)(blk >> 32);
+        g.ctr[2] = (uint32_t)stream1, g.ctr[3] = (uint32_t)(stream1 >> 32);
+        skip = used & 7u, drawn = 0, active = true;
     }
-    digits_out[0] = sb * z[0] + qd[0] * z[last] + vd[0];
-    for (uint32_t i = 1; i < last; i++) digits_out[i] = sb * z[i] - z[i - 1] + qd[i] * z[last] + vd[i];
-    digits_out[last] = qd[last] * z[last] - z[last - 1] + vd[last];
+};
+
+// K Gaussian integers D(0, sigma) from the streams (poly + 1, coeff_k + 1, 0, kDomGauss), coeff_k = coeff0 + k * stride.
+// The coefficient is the nonce of these streams (stream2 = 0), so all K share one HChaCha20 sub-key.
+template <int K>
+GP_HD void gauss_integers_batch(const Seed256 &seed, double sigma, uint64_t global_poly, uint64_t coeff0, uint64_t stride, int64_t *z) {
+    uint32_t key[8];
+    {
+        ChaChaStream s;
+        s.open(seed, global_poly + 1, coeff0 + 1, 0, kDomGauss);
+#pragma unroll
+        for (int i = 0; i < 8; i++) key[i] = s.key[i];
+    }
+    BatchLane ln;
+    ln.start();
+    for (;;) {
+        // transitions that need no stream word: a finished draw ends its task; a lane between tasks takes the next one
+        // when the warp is at a block boundary.  Every lane that stays in the loop reaches g.next() on every trip.
+        for (;;) {
+            if (ln.active) {
+                if (!ln.km.done()) break;
+                z[ln.cur++] = ln.km.result, ln.active = false;
+            } else {
+                if (ln.cur >= (uint32_t)K || !ln.at_boundary()) break;
+                ln.resume(key, global_poly + 1, coeff0 + (uint64_t)ln.cur * stride + 1, 0);
+                ln.km.begin(0.0, sigma);
+            }
+        }
+        if (!ln.active && ln.cur >= (uint32_t)K) break;
+        const uint64_t w = ln.g.next();
+        if (ln.active) ln.km.step(w);  // else: waiting for the boundary, the word is dropped
+    }
+}
+
+// K G-lattice tasks of one (poly, tower): coefficients coeff0 + k * stride, source residues values[k]; digits_out[k * DMAX + i]
+template <int DMAX, int K>
+GP_HD void gq_sample_digits_batch(const Seed256 &seed, const uint64_t *values, uint64_t q, uint32_t base_bits, uint32_t dpt, double c,
+                                  uint32_t tower, uint64_t poly, uint64_t coeff0, uint64_t stride, int64_t *digits_out) {
+    GqTower<DMAX> tw;
+    tw.init(q, base_bits, dpt, c);
+    uint32_t keys[K][8];
+    double a[K][DMAX];
+    int64_t z[K][DMAX];
+    for (int k = 0; k < K; k++) {  // up front, all lanes active: sub-key, continuous normals, target
+        ChaChaStream s;
+        s.open(seed, (uint64_t)tower + 1, poly + 1, coeff0 + (uint64_t)k * stride + 1, kDomGadget);
+#pragma unroll
+        for (int i = 0; i < 8; i++) keys[k][i] = s.key[i];
+        tw.target(s, values[k], a[k]);
+    }
+    const uint32_t used = 2 * dpt;  // words behind the dpt normals (ChaChaStream::normal takes two)
+    BatchLane ln;
+    ln.start();
+    for (;;) {
+        for (;;) {  // word-free transitions, as in gauss_integers_batch; a finished draw may also start the task's next draw
+            if (ln.active) {
+                if (!ln.km.done()) break;
+                double mean, sd;
+                if (tw.chain(ln.drawn, ln.km.result, a[ln.cur], z[ln.cur], mean, sd)) {
+                    ln.km.begin(mean, sd);
+                    ++ln.drawn;
+                } else {
+                    ++ln.cur, ln.active = false;
+                }
+            } else {
+                if (ln.cur >= (uint32_t)K || !ln.at_boundary()) break;
+                ln.resume(keys[ln.cur], (uint64_t)tower + 1, poly + 1, used);
+                ln.km.begin(-a[ln.cur][tw.last] / tw.cv[tw.last], tw.sigma / tw.cv[tw.last]);
+            }
+        }
+        if (!ln.active && ln.cur >= (uint32_t)K) break;
+        const uint64_t w = ln.g.next();
+        if (ln.active) {
+            if (ln.skip) --ln.skip;  // a word the up-front phase has used
+            else ln.km.step(w);
+        }
+    }
+    for (int k = 0; k < K; k++) tw.digits(values[k], z[k], digits_out + (size_t)k * DMAX);
 }
 
 // ---- perturbation p1: per-coefficient 2d x 2d conditional Gaussian ----------------------
@@ -421,12 +585,29 @@ GP_HD void p1_sample_column(LoadTp2 centred_tp2, const Seed256 &seed, uint32_t m
     ChaChaStream g;
     g.open(seed, (uint64_t)col + 1, (uint64_t)coeff + 1, 0, kDomPerturb);
     for (uint32_t r = 0; r < m; r++) mean[r * st] = c_scale * (double)centred_tp2(r);
-    for (int t = (int)m - 1; t >= 0; --t) {
-        const double mu = mean[(size_t)t * st];
-        const int64_t zt = karney_integer(g, mu, sd[(size_t)t * n + coeff]);
-        zs[(size_t)t * st] = zt;
-        const double delta = (double)zt - mu;
-        for (int i = 0; i < t; i++) mean[(size_t)i * st] += GP_UPD(t, i) * delta;
+    // rows m-1 .. 0 as one word-per-trip loop (see karney_integer)
+    if (m == 0) return;
+    KarneyMachine km;
+    int t = (int)m - 1;
+    double mu = mean[(size_t)t * st];
+    km.begin(mu, sd[(size_t)t * n + coeff]);
+    for (;;) {
+        bool fin = false;
+        while (km.done()) {
+            const int64_t zt = km.result;
+            zs[(size_t)t * st] = zt;
+            const double delta = (double)zt - mu;
+            for (int i = 0; i < t; i++) mean[(size_t)i * st] += GP_UPD(t, i) * delta;
+            if (t == 0) {
+                fin = true;
+                break;
+            }
+            --t;
+            mu = mean[(size_t)t * st];
+            km.begin(mu, sd[(size_t)t * n + coeff]);
+        }
+        if (fin) break;
+        km.step(g.next());
     }
 #undef GP_UPD
 }
@@ -497,6 +678,60 @@ __global__ void __launch_bounds__(128) gauss_samp_gq_kernel(const T *__restrict_
         T *p = out + out_poly * limbs * (size_t)n + coeff;
         for (uint32_t l = 0; l < limbs; l++) p[(size_t)l * n] = small_to_residue<T>(digits[dg], lc[l]);
     }
+}
+
+// ---- lane-balanced kernels: a warp owns 32 K consecutive coefficients of one polynomial (n % (32 K) == 0); lane l runs
+// coefficients c0 + l + 32 k through gauss_integers_batch / gq_sample_digits_batch, so for every k the warp reads and
+// writes 32 consecutive words.  The bodies are GP_HD so the host harness walks the same index arithmetic.
+template <typename T, int K>
+GP_HD void sample_gauss_batch_thread(size_t tid, T *__restrict__ dst, const SampleGeom &g, double sigma, const Seed256 &seed,
+                                     const LimbConst<T> *__restrict__ lc) {
+    const size_t base = (tid >> 5) * (size_t)(32 * K);
+    if (base >= g.polys * g.n) return;
+    const size_t poly = base / g.n, c0 = base - poly * g.n + (tid & 31);
+    const size_t row = poly / g.local_cols, col = poly - row * g.local_cols;
+    int64_t z[K];
+    gauss_integers_batch<K>(seed, sigma, row * g.full_cols + g.col_offset + col, c0, 32, z);
+    for (int k = 0; k < K; k++) {
+        T *p = dst + poly * g.limbs * (size_t)g.n + c0 + 32 * (size_t)k;
+        for (uint32_t l = 0; l < g.limbs; l++) p[(size_t)l * g.n] = small_to_residue<T>(z[k], lc[l]);
+    }
+}
+template <typename T, int K>
+GP_HD void gauss_samp_gq_batch_thread(size_t tid, const T *__restrict__ src, T *__restrict__ out, size_t src_polys, size_t src_cols,
+                                      uint32_t n, uint32_t limbs, uint32_t base_bits, uint32_t dpt, double c, const Seed256 &seed,
+                                      const LimbConst<T> *__restrict__ lc) {
+    constexpr int DMAX = 8;
+    const size_t base = (tid >> 5) * (size_t)(32 * K);
+    if (base >= src_polys * limbs * n) return;
+    const size_t pl = base / n, c0 = base - pl * n + (tid & 31);
+    const size_t poly = pl / limbs;
+    const uint32_t tower = (uint32_t)(pl - poly * limbs);
+    uint64_t values[K];
+    for (int k = 0; k < K; k++) values[k] = (uint64_t)src[pl * n + c0 + 32 * (size_t)k];
+    int64_t digits[K * DMAX];
+    gq_sample_digits_batch<DMAX, K>(seed, values, (uint64_t)lc[tower].q, base_bits, dpt, c, tower, poly, c0, 32, digits);
+    const size_t row = poly / src_cols, col = poly - row * src_cols;
+    const size_t ell = (size_t)dpt * limbs;
+    for (int k = 0; k < K; k++)
+        for (uint32_t dg = 0; dg < dpt; dg++) {
+            const size_t out_poly = (row * ell + (size_t)tower * dpt + dg) * src_cols + col;
+            T *p = out + out_poly * limbs * (size_t)n + c0 + 32 * (size_t)k;
+            for (uint32_t l = 0; l < limbs; l++) p[(size_t)l * n] = small_to_residue<T>(digits[k * DMAX + dg], lc[l]);
+        }
+}
+template <typename T, int K>
+__global__ void __launch_bounds__(128) sample_gauss_batch_kernel(T *__restrict__ dst, SampleGeom g, double sigma, Seed256 seed,
+                                                                 const LimbConst<T> *__restrict__ lc) {
+    sample_gauss_batch_thread<T, K>((size_t)blockIdx.x * blockDim.x + threadIdx.x, dst, g, sigma, seed, lc);
+}
+template <typename T, int K>
+__global__ void __launch_bounds__(128) gauss_samp_gq_batch_kernel(const T *__restrict__ src, T *__restrict__ out, size_t src_polys,
+                                                                  size_t src_cols, uint32_t n, uint32_t limbs, uint32_t base_bits,
+                                                                  uint32_t dpt, double c, Seed256 seed,
+                                                                  const LimbConst<T> *__restrict__ lc) {
+    gauss_samp_gq_batch_thread<T, K>((size_t)blockIdx.x * blockDim.x + threadIdx.x, src, out, src_polys, src_cols, n, limbs, base_bits,
+                                     dpt, c, seed, lc);
 }
 
 // covariance factorisation: one thread per coefficient (limb 0 of A, B, D in coefficient form)

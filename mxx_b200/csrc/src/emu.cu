@@ -521,6 +521,40 @@ template <typename T> int do_sample_p1(int logn, uint32_t limbs, const uint64_t 
         }
     return 0;
 }
+// the lane-balanced kernels' thread bodies, walked over their thread index space (K tasks per thread, tests only)
+template <typename T, int K>
+int do_sample_gauss_batched(int logn, uint32_t limbs, const uint64_t *moduli, double sigma, const uint64_t *seed, size_t rows,
+                            size_t local_cols, size_t full_cols, size_t col_offset, uint64_t *out) {
+    Emu<T> e(logn, limbs, moduli);
+    Seed256 sd;
+    for (int i = 0; i < 4; i++) sd.w[i] = seed[i];
+    SampleGeom g;
+    g.polys = rows * local_cols, g.local_cols = local_cols, g.full_cols = full_cols, g.col_offset = col_offset;
+    g.n = 1u << logn, g.limbs = limbs;
+    if (g.n % (32 * K)) return 1;
+    std::vector<T> dst(g.polys * limbs * g.n);
+    const size_t threads = g.polys * g.n / K;
+    for (size_t tid = 0; tid < threads; tid++) sample_gauss_batch_thread<T, K>(tid, dst.data(), g, sigma, sd, e.tab.limb.data());
+    for (size_t i = 0; i < dst.size(); i++) out[i] = (uint64_t)dst[i];
+    return 0;
+}
+template <typename T, int K>
+int do_gauss_samp_batched(int logn, uint32_t limbs, const uint64_t *moduli, const uint64_t *src, size_t rows, size_t cols,
+                          uint32_t base_bits, uint32_t dpt, double c, const uint64_t *seed, uint64_t *out) {
+    Emu<T> e(logn, limbs, moduli);
+    const uint32_t n = 1u << logn;
+    if (n % (32 * K) || dpt > 8) return 1;
+    Seed256 sd;
+    for (int i = 0; i < 4; i++) sd.w[i] = seed[i];
+    const size_t polys = rows * cols;
+    std::vector<T> s(polys * limbs * n), dst(polys * dpt * limbs * limbs * n);
+    for (size_t i = 0; i < s.size(); i++) s[i] = (T)src[i];
+    const size_t threads = polys * limbs * n / K;
+    for (size_t tid = 0; tid < threads; tid++)
+        gauss_samp_gq_batch_thread<T, K>(tid, s.data(), dst.data(), polys, cols, n, limbs, base_bits, dpt, c, sd, e.tab.limb.data());
+    for (size_t i = 0; i < dst.size(); i++) out[i] = (uint64_t)dst[i];
+    return 0;
+}
 }  // namespace
 
 extern "C" {
@@ -547,6 +581,52 @@ int emu_gauss_samp(int force_wide, int logn, uint32_t limbs, const uint64_t *mod
             return do_gauss_samp<uint64_t>(logn, limbs, moduli, src, rows, cols, base_bits, dpt, c, seed, out);
         return do_gauss_samp<uint32_t>(logn, limbs, moduli, src, rows, cols, base_bits, dpt, c, seed, out);
     } catch (...) { return 1; }
+}
+#define EMU_BATCH_SWITCH(CALL)          \
+    switch (batch) {                    \
+        case 2: return CALL(2);         \
+        case 4: return CALL(4);         \
+        case 8: return CALL(8);         \
+        default: return 1;              \
+    }
+int emu_sample_gauss_batched(int batch, int force_wide, int logn, uint32_t limbs, const uint64_t *moduli, double sigma,
+                             const uint64_t *seed, size_t rows, size_t local_cols, size_t full_cols, size_t col_offset, uint64_t *out) {
+    if (force_wide || wide_for(moduli, limbs)) {
+#define EMU_CALL(K) do_sample_gauss_batched<uint64_t, K>(logn, limbs, moduli, sigma, seed, rows, local_cols, full_cols, col_offset, out)
+        EMU_BATCH_SWITCH(EMU_CALL)
+#undef EMU_CALL
+    }
+#define EMU_CALL(K) do_sample_gauss_batched<uint32_t, K>(logn, limbs, moduli, sigma, seed, rows, local_cols, full_cols, col_offset, out)
+    EMU_BATCH_SWITCH(EMU_CALL)
+#undef EMU_CALL
+}
+int emu_gauss_samp_batched(int batch, int force_wide, int logn, uint32_t limbs, const uint64_t *moduli, const uint64_t *src, size_t rows,
+                           size_t cols, uint32_t base_bits, uint32_t dpt, double c, const uint64_t *seed, uint64_t *out) {
+    if (force_wide || wide_for(moduli, limbs)) {
+#define EMU_CALL(K) do_gauss_samp_batched<uint64_t, K>(logn, limbs, moduli, src, rows, cols, base_bits, dpt, c, seed, out)
+        EMU_BATCH_SWITCH(EMU_CALL)
+#undef EMU_CALL
+    }
+#define EMU_CALL(K) do_gauss_samp_batched<uint32_t, K>(logn, limbs, moduli, src, rows, cols, base_bits, dpt, c, seed, out)
+    EMU_BATCH_SWITCH(EMU_CALL)
+#undef EMU_CALL
+}
+// stream words each (poly, tower, coeff) task of the G-lattice sampler consumes, in the kernel's thread order: the input of
+// the warp model in tests/test_samplers.py (a warp runs max-over-lanes trips; a lane is busy for its own count)
+int emu_gauss_samp_words(int logn, uint32_t limbs, const uint64_t *moduli, const uint64_t *src, size_t polys, uint32_t base_bits,
+                         uint32_t dpt, double c, const uint64_t *seed, uint32_t *words) {
+    if (dpt > 8) return 1;
+    const size_t n = (size_t)1 << logn;
+    Seed256 sd;
+    for (int i = 0; i < 4; i++) sd.w[i] = seed[i];
+    for (size_t poly = 0; poly < polys; poly++)
+        for (uint32_t tower = 0; tower < limbs; tower++)
+            for (size_t ci = 0; ci < n; ci++) {
+                int64_t digits[8];
+                const size_t idx = (poly * limbs + tower) * n + ci;
+                gq_sample_digits<8>(sd, src[idx], moduli[tower], base_bits, dpt, c, tower, poly, ci, digits, &words[idx]);
+            }
+    return 0;
 }
 int emu_sample_p1(int force_wide, int logn, uint32_t limbs, const uint64_t *moduli, const uint64_t *a, const uint64_t *b,
                   const uint64_t *dm, const uint64_t *tp2, uint32_t d, size_t cols, double sigma, double s, double dgg,

@@ -40,13 +40,24 @@ template <class Launch> int for_each_matmul_slab(const gp::MatmulGeom &g, int TR
     return 0;
 }
 
+// Launch order of the row-tiled products (TR >= 2): column tiles fastest, so that the CTAs in flight share their slices of
+// the left operand (arith.cuh matmul_kernel COLS_FAST).  MXX_MATMUL_COLS_FAST=0 keeps the slot chunks fastest (A/B runs).
+bool matmul_cols_fast(unsigned slot_ctas) {
+    static const int knob = getenv("MXX_MATMUL_COLS_FAST") ? atoi(getenv("MXX_MATMUL_COLS_FAST")) : 1;
+    return knob != 0 && slot_ctas <= kMaxGridYZ;
+}
+
 template <typename T, int V, int TR, int TC, int UNROLL = 2, int NT = 128>
 int launch_matmul_tile(GpuContext *ctx, T *out, const T *A, const T *B, const gp::MatmulGeom &g) {
     const unsigned threads = NT;
     const unsigned per_limb = (unsigned)(((size_t)ctx->N / V + threads - 1) / threads);
     return for_each_matmul_slab(g, TR, TC, (size_t)g.limbs << g.logn, [&](const gp::MatmulGeom &s, size_t a_off, size_t o_off) {
-        dim3 grid(s.limbs * per_limb, (s.cols + TC - 1) / TC, (s.rows + TR - 1) / TR);
-        gp::matmul_kernel<T, V, TR, TC, UNROLL, NT><<<grid, threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, (const gp::LimbConst<T> *)ctx->d_limb);
+        const unsigned slot_ctas = s.limbs * per_limb, col_tiles = (s.cols + TC - 1) / TC, row_tiles = (s.rows + TR - 1) / TR;
+        const auto *lc = (const gp::LimbConst<T> *)ctx->d_limb;
+        if (TR >= 2 && col_tiles > 1 && matmul_cols_fast(slot_ctas))
+            gp::matmul_kernel<T, V, TR, TC, UNROLL, NT, true><<<dim3(col_tiles, slot_ctas, row_tiles), threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, lc);
+        else
+            gp::matmul_kernel<T, V, TR, TC, UNROLL, NT, false><<<dim3(slot_ctas, col_tiles, row_tiles), threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, lc);
         gp::count_launch();
         GP_CHECK_LAUNCH("matmul_kernel");
         return 0;
@@ -58,8 +69,12 @@ int launch_matmul_f64_tile(GpuContext *ctx, uint64_t *out, const uint64_t *A, co
     const unsigned threads = NT;
     const unsigned per_limb = (unsigned)(((size_t)ctx->N / V + threads - 1) / threads);
     return for_each_matmul_slab(g, TR, TC, (size_t)g.limbs << g.logn, [&](const gp::MatmulGeom &s, size_t a_off, size_t o_off) {
-        dim3 grid(s.limbs * per_limb, (s.cols + TC - 1) / TC, (s.rows + TR - 1) / TR);
-        gp::matmul_f64_kernel<V, TR, TC, UNROLL, NT><<<grid, threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, (const gp::LimbConst<gp::F64> *)ctx->d_limb_f64);
+        const unsigned slot_ctas = s.limbs * per_limb, col_tiles = (s.cols + TC - 1) / TC, row_tiles = (s.rows + TR - 1) / TR;
+        const auto *lc = (const gp::LimbConst<gp::F64> *)ctx->d_limb_f64;
+        if (TR >= 2 && col_tiles > 1 && matmul_cols_fast(slot_ctas))
+            gp::matmul_f64_kernel<V, TR, TC, UNROLL, NT, true><<<dim3(col_tiles, slot_ctas, row_tiles), threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, lc);
+        else
+            gp::matmul_f64_kernel<V, TR, TC, UNROLL, NT, false><<<dim3(slot_ctas, col_tiles, row_tiles), threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, lc);
         gp::count_launch();
         GP_CHECK_LAUNCH("matmul_f64_kernel");
         return 0;

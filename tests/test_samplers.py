@@ -11,6 +11,7 @@ the same relations, and the full trapdoor -> preimage flow A x = u.
 """
 import ctypes as C
 import os
+import sys
 
 import numpy as np
 import pytest
@@ -251,6 +252,66 @@ def test_emu_p1_matches_oracle(emu):
     assert (zc == zc[:, :, :1, :]).all() and np.abs(zc).max() < 12 * s
 
 
+# ---------------------------------------------------------------- lane-balanced drivers (K tasks per thread): same samples
+def _batched_emu(emu):
+    emu.emu_gauss_samp_batched.argtypes = [C.c_int] + list(emu.emu_gauss_samp.argtypes)
+    emu.emu_sample_gauss_batched.argtypes = [C.c_int, C.c_int, C.c_int, C.c_uint32, u64p, C.c_double, u64p] + [C.c_size_t] * 4 + [u64p]
+    emu.emu_gauss_samp_words.argtypes = [C.c_int, C.c_uint32, u64p, u64p, C.c_size_t, C.c_uint32, C.c_uint32, C.c_double, u64p,
+                                         C.POINTER(C.c_uint32)]
+    return emu
+
+
+@pytest.mark.parametrize("n,depth,bits,bb", [(256, 3, 24, 12), (256, 2, 24, 5), (256, 2, 51, 17), (256, 2, 59, 8), (512, 2, 28, 14)])
+def test_emu_batched_samplers_draw_the_same_samples(emu, n, depth, bits, bb):
+    """gauss_integers_batch / gq_sample_digits_batch (a thread runs K tasks through one word-per-trip loop and resumes each
+    stream on a key-stream block boundary) against the one-task forms, through the kernels' own thread bodies."""
+    emu = _batched_emu(emu)
+    plan = plan_for(n, depth, bits)
+    mod, seed = np.array(plan.moduli, dtype=np.uint64), orc.seed_words([5, 6, 7, bb])
+    src, dpt, logn = plan.uniform(2, 2, seed=78), plan.dpt(bb), n.bit_length() - 1
+    for scale in (1.0, 37.0):
+        c = ((1 << bb) + 1.0) * SIGMA * scale
+        z = np.zeros((2 * dpt * plan.L, 2, plan.L, n), dtype=np.uint64)
+        assert emu.emu_gauss_samp(0, logn, plan.L, p(mod), p(src), 2, 2, bb, dpt, c, p(seed), p(z)) == 0
+        for k in (2, 4, 8):
+            zb = np.zeros_like(z)
+            assert emu.emu_gauss_samp_batched(k, 0, logn, plan.L, p(mod), p(src), 2, 2, bb, dpt, c, p(seed), p(zb)) == 0
+            assert np.array_equal(z, zb), (scale, k)
+    for sg in (SIGMA, 2.5e7, 0.3):
+        want = np.zeros((2, 2, plan.L, n), dtype=np.uint64)
+        assert emu.emu_sample_distribution(0, logn, plan.L, p(mod), DIST_GAUSS, sg, p(seed), 2, 2, 5, 1, p(want)) == 0
+        for k in (2, 4, 8):
+            got = np.zeros_like(want)
+            assert emu.emu_sample_gauss_batched(k, 0, logn, plan.L, p(mod), sg, p(seed), 2, 2, 5, 1, p(got)) == 0
+            assert np.array_equal(want, got), (sg, k)
+
+
+def test_warp_model_of_the_g_lattice_sampler(emu):
+    """The numbers DESIGN.md quotes for the sampler's lane utilisation: stream words per (poly, tower, coeff) task of the
+    C5-shaped G-lattice sampler (two digits per tower), a warp of one-task lanes runs max-over-lanes trips, a warp of
+    K-task lanes runs the longest sum (each task starts on a multiple of 8 trips)."""
+    emu = _batched_emu(emu)
+    n, depth, bits, bb = 4096, 3, 24, 12
+    plan = plan_for(n, depth, bits)
+    mod, seed = np.array(plan.moduli, dtype=np.uint64), orc.seed_words([5, 6, 7, 8])
+    src = plan.uniform(1, 2, seed=78)
+    w = np.zeros(src.size, dtype=np.uint32)
+    c = ((1 << bb) + 1.0) * SIGMA
+    assert emu.emu_gauss_samp_words(12, plan.L, p(mod), p(src), 2, bb, plan.dpt(bb), c, p(seed), w.ctypes.data_as(C.POINTER(C.c_uint32))) == 0
+    assert 35 < w.mean() < 50 and w.min() >= 4 + 2 * 3  # two normals (4 words), two integer draws
+
+    def busy_lanes(k):
+        warps = w.size // (32 * k)
+        per = w[: warps * 32 * k].reshape(warps, k, 32).astype(np.int64)
+        t = np.zeros((warps, 32), dtype=np.int64)
+        for i in range(k):
+            t = (t + 7) // 8 * 8 + per[:, i, :]
+        return 32.0 * per.sum() / (32.0 * t.max(1).sum())
+
+    lanes = {k: busy_lanes(k) for k in (1, 4, 8)}
+    assert 11 < lanes[1] < 14 and 17 < lanes[4] < 20 and 19.5 < lanes[8] < 23, lanes
+
+
 # ---------------------------------------------------------------- golden vectors from the reference's CUDA library
 def _golden():
     if not os.path.exists(GOLDEN):
@@ -364,6 +425,45 @@ def test_gpu_matches_reference_cuda_samplers(case):
     for k, v in mine.items():
         assert np.array_equal(v, g[f"{key}/{k}"]), k
     assert M is not None
+
+
+BATCH_KNOB_SCRIPT = """
+import sys
+import numpy as np
+sys.path.insert(0, {root!r})
+from mxx_b200 import GpuDCRTPolyMatrix as M, GpuDCRTPolyParams
+from mxx_b200.matrix import DIST_GAUSS
+from oracle import oracle as orc
+out = {{}}
+for n, depth, bits, bb in [(1024, 3, 24, 12), (512, 2, 51, 17), (256, 2, 28, 7)]:
+    moduli = orc.prime_chain(n, bits, depth)
+    params, plan = GpuDCRTPolyParams(n, moduli, bb), orc.Plan(n, moduli)
+    seed = [n, bits, 3, 4]
+    key = "n%d_b%d" % (n, bits)
+    out[key + "_gauss"] = M.sample_distribution(params, 2, 3, DIST_GAUSS, 4.578, seed).to_rns()
+    out[key + "_gauss_big"] = M.sample_distribution_columns(params, 2, 5, 1, 3, DIST_GAUSS, 3.1e7, seed).to_rns()
+    src = plan.uniform(2, 2, seed=9)
+    out[key + "_gq"] = M.from_rns(params, src, False).gauss_samp_gq_arb_base(((1 << bb) + 1.0) * 4.578, 4.578, seed).to_rns()
+np.savez({path!r}, **out)
+print("sampler knob ok")
+"""
+
+
+@pytest.mark.gpu
+def test_gpu_sampler_batch_knob_keeps_samples(tmp_path):
+    """MXX_SAMPLER_BATCH = 1 (one task per thread) / 2 / 4 / 8 tasks per lane: the same matrices, word for word."""
+    import subprocess
+
+    got = {}
+    for k in ("1", "2", "4", "8"):
+        path = str(tmp_path / f"k{k}.npz")
+        run = subprocess.run([sys.executable, "-c", BATCH_KNOB_SCRIPT.format(root=ROOT, path=path)], env=dict(os.environ, MXX_SAMPLER_BATCH=k),
+                             capture_output=True, text=True, timeout=900)
+        assert run.returncode == 0 and "sampler knob ok" in run.stdout, run.stderr[-2000:]
+        got[k] = dict(np.load(path))
+    for k in ("2", "4", "8"):
+        for name, v in got["1"].items():
+            assert np.array_equal(v, got[k][name]), (k, name)
 
 
 @pytest.mark.gpu
