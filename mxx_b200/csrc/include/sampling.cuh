@@ -171,21 +171,44 @@ GP_HD int64_t centred(uint64_t x, uint64_t q) {
 // profiles/r01_ncu_sampler.txt).  With one word per step every lane of a warp draws at the same instruction,
 // key-stream blocks are refilled by all lanes together, and only the few-instruction case bodies diverge.
 // The sequence of words each decision consumes is unchanged, so samples are identical to the nested-loop form.
+// What a draw needs from its deviation alone: callers that draw many integers with the same deviation (every task of a
+// sample_distribution launch; the first / the later draws of every G-lattice task of a tower) set it up once, with all lanes
+// active, instead of dividing 2^64 by the span inside the rejection loop.
+struct KarneyScale {
+    double sd;
+    int64_t span;     // ceil(sd)
+    uint64_t span_m;  // floor((2^64 - 1) / span): `word % span` without a 64-bit division per attempt
+    bool valid;       // false: the draw degenerates to llround(mean)
+    GP_HD void init(double sd_) {
+        sd = sd_, span = 0, span_m = 0;
+        valid = sd > 0.0 && isfinite(sd);
+        if (valid) {
+            span = (int64_t)ceil(sd);
+            valid = span > 0;
+        }
+        if (valid) span_m = ~0ULL / (uint64_t)span;
+    }
+};
+
 struct KarneyMachine {
     enum : uint32_t { kGH0, kGH1, kGH2, kPH0, kPH1, kPH2, kSign, kJ, kB0, kB1, kFb1, kFb2, kDone };
     uint32_t st;
     int32_t k, n, h, bn, tries;
     double mean, sd, hv, x, x0, y, z, bthr;  // bthr = (2k + x) / (2k + 2), fixed for all B tests of one attempt
     int64_t i0, j, sgn, span, result;
+    uint64_t span_m;
 
     GP_HD bool done() const { return st == kDone; }
     GP_HD void finish(int64_t r) { result = r, st = kDone; }
-    GP_HD void begin(double mean_, double sd_) {
-        mean = mean_, sd = sd_, tries = 0;
-        if (!(sd > 0.0) || !isfinite(mean) || !isfinite(sd)) return finish((int64_t)llround(mean));
-        span = (int64_t)ceil(sd);
-        if (span <= 0) return finish((int64_t)llround(mean));
+    GP_HD void begin(double mean_, const KarneyScale &sc) {
+        mean = mean_, sd = sc.sd, span = sc.span, span_m = sc.span_m, tries = 0;
+        if (!sc.valid || !isfinite(mean)) return finish((int64_t)llround(mean));
         restart();
+    }
+    GP_HD void begin(double mean_, double sd_) {
+        KarneyScale sc;
+        sc.init(sd_);
+        begin(mean_, sc);
     }
     // top of the rejection loop (65536 attempts, then the continuous fall-back)
     GP_HD void restart() {
@@ -243,20 +266,27 @@ struct KarneyMachine {
             return;
         }
         switch (st) {
-            case kSign: {
+            case kSign:
+                // only the sign is taken here; everything that follows from it waits for kJ, so that the divisions of an
+                // attempt sit in ONE case body (with a dozen busy lanes most trips find some lane in kSign and some lane in
+                // kJ, and a warp pays for every body any of its lanes needs)
                 sgn = (w & 1ULL) ? 1 : -1;
+                st = kJ;
+                break;
+            case kJ: {
                 const double di0 = sd * (double)k + (double)sgn * mean;
                 i0 = (int64_t)ceil(di0);
                 x0 = ((double)i0 - di0) / sd;
-                st = kJ;
-                break;
-            }
-            case kJ:
-                j = (int64_t)(w % (uint64_t)span);
+                // j = w % span through the precomputed floor((2^64 - 1) / span): the estimate never exceeds the quotient
+                const uint64_t us = (uint64_t)span;
+                uint64_t r = w - mulhi(w, span_m) * us;
+                while (r >= us) r -= us;
+                j = (int64_t)r;
                 x = x0 + (double)j / sd;
                 if (!(x < 1.0) || (x == 0.0 && sgn < 0 && k == 0)) restart();
                 else h = k + 1, bthr = (2.0 * (double)k + x) / (double)(2 * k + 2), b_check();
                 break;
+            }
             case kFb1:
                 hv = u, st = kFb2;
                 break;
@@ -315,14 +345,13 @@ GP_HD uint64_t draw_uniform_residue(const Seed256 &seed, uint64_t global_poly, u
 // ---- G-lattice sampler, one (poly, coeff, tower) --------------------------------------
 // Writes the dpt signed digits x with  sum_i x_i b^i == value (mod q)  and x ~ D_{Lambda, c}.
 // DMAX bounds the local arrays (8 covers every base >= ceil(crt_bits/8); 64 is the ABI limit).
-// The three pieces below are shared by the one-task form (gq_sample_digits) and the lane-balanced form
-// (gq_sample_digits_batch), so both evaluate the same floating-point expressions.
 template <int DMAX> struct GqTower {  // what depends on (q, base, dpt, c) only
     uint32_t base_bits, dpt, last;
     uint64_t base;
     double bf, sigma, kf;
     int64_t qd[DMAX];
     double cv[DMAX];
+    KarneyScale first, later;  // deviations of z[last] (sigma / cv[last]) and of the other draws (sigma)
     GP_HD void init(uint64_t q, uint32_t base_bits_, uint32_t dpt_, double c) {
         base_bits = base_bits_, dpt = dpt_, last = dpt_ - 1;
         base = 1ULL << base_bits;
@@ -336,6 +365,8 @@ template <int DMAX> struct GqTower {  // what depends on (q, base, dpt, c) only
         }
         cv[0] = (double)qd[0] / bf;
         for (uint32_t i = 1; i < dpt; i++) cv[i] = (cv[i - 1] + (double)qd[i]) / bf;
+        first.init(sigma / cv[last]);
+        later.init(sigma);
     }
     GP_HD int64_t value_digit(uint64_t value, uint32_t i) const { return (int64_t)((value >> (base_bits * i)) & (base - 1)); }
     // the running target a[] of one task: dpt continuous normals (the first 2 dpt words of the stream), the perturbation
@@ -360,8 +391,8 @@ template <int DMAX> struct GqTower {  // what depends on (q, base, dpt, c) only
         }
     }
     // a finished draw of the chain z[last], z[0], .., z[last-1] (`drawn` = draws finished before this one); returns false
-    // when it was the last one, otherwise the (mean, deviation) of the next draw
-    GP_HD bool chain(uint32_t drawn, int64_t r, double *a, int64_t *z, double &mean, double &sd) const {
+    // when it was the last one, otherwise the mean of the next draw
+    GP_HD bool chain(uint32_t drawn, int64_t r, double *a, int64_t *z, double &mean) const {
         if (drawn == 0) {
             z[last] = r;
             for (uint32_t i = 0; i < dpt; i++) a[i] += (double)r * cv[i];
@@ -369,7 +400,7 @@ template <int DMAX> struct GqTower {  // what depends on (q, base, dpt, c) only
             z[drawn - 1] = r;
         }
         if (drawn == last) return false;
-        mean = -a[drawn], sd = sigma;
+        mean = -a[drawn];  // deviation: sigma (`later`)
         return true;
     }
     GP_HD void digits(uint64_t value, const int64_t *z, int64_t *out) const {
@@ -399,16 +430,16 @@ GP_HD void gq_sample_digits(const Seed256 &seed, uint64_t value, uint64_t q, uin
     {
         KarneyMachine km;
         uint32_t drawn = 0;
-        km.begin(-a[tw.last] / tw.cv[tw.last], tw.sigma / tw.cv[tw.last]);
+        km.begin(-a[tw.last] / tw.cv[tw.last], tw.first);
         for (;;) {
             bool fin = false;
             while (km.done()) {  // also a draw that needs no word at all (degenerate deviation)
-                double mean, sd;
-                if (!tw.chain(drawn, km.result, a, z, mean, sd)) {
+                double mean;
+                if (!tw.chain(drawn, km.result, a, z, mean)) {
                     fin = true;
                     break;
                 }
-                km.begin(mean, sd);
+                km.begin(mean, tw.later);
                 ++drawn;
             }
             if (fin) break;
@@ -420,18 +451,22 @@ GP_HD void gq_sample_digits(const Seed256 &seed, uint64_t value, uint64_t q, uin
 }
 
 // ---- lane-balanced form: a thread runs K tasks through ONE word-per-trip loop --------------------------------------------
-// The number of words a draw consumes is long-tailed (G-lattice task with two digits: mean 42, 99th percentile 124), so a
-// warp whose lanes own one task each runs for the longest of 32 tasks: 12 of 32 lanes busy on average (warp model over
-// the word counts of real streams, tests/test_samplers.py).  Here a lane owns K tasks and moves to its next one as soon
-// as the current one is done, so the warp runs for the longest SUM of K: 18 of 32 lanes busy for K = 4, 21 for K = 8.
-// What keeps this in lock step:
-//   * everything that is not the rejection loop runs for all K tasks up front (HChaCha20 key derivation; for the G-lattice
-//     sampler also the continuous normals — log, cos, sqrt — and the target a[]) or at the end (digits, RNS reduction,
-//     stores), with all lanes active;
-//   * a lane takes its next task only on a trip at which the whole warp is at a key-stream block boundary, and first skips
-//     the words the up-front phase has already used, so the position inside the block stays equal across the warp
-//     and all lanes run the ChaCha permutation together (cost: 3.5 idle trips per task on average).
+// The number of words a draw consumes is long-tailed (one Gaussian integer: mean 19 words; a G-lattice task with two digits:
+// mean 42, 99th percentile 124), so a warp whose lanes own one task each runs for the longest of 32 tasks: 12 of 32 lanes
+// in the loop on average (warp model over the word counts of real streams, tests/test_samplers.py).  Here a lane owns K
+// tasks and moves to its next one as soon as the current one is done, so the warp runs for the longest SUM of K: 18 of 32
+// lanes for K = 4, 21 for K = 8.  What keeps this in lock step:
+//   * everything that is not the rejection loop (HChaCha20 key derivation, RNS reduction, stores) runs for all K tasks up
+//     front or at the end, with all lanes active;
+//   * a lane takes its next task only on a trip at which the whole warp is at a key-stream block boundary (and would first
+//     skip the words a task's up-front phase had used), so the position inside the block stays equal across the warp and all
+//     lanes run the ChaCha permutation together (cost: 3.5 idle trips per task on average).
 // Each task reads exactly the words the one-task form reads, so the samples are identical.
+// Measured on B200 (ncu, profiles/r02_sampler_lab.txt): the Gaussian matrix of the C5 preimage (16.4 M draws) 12.2 ms with one
+// task per thread, 10.9 ms for K = 4, 8.7 ms for K = 8 (7.5 G instead of 10.1 G warp instructions).  The same driver for the
+// G-lattice sampler was built and measured and is NOT kept: its task switches (mean -a/cv, a += z cv, the next draw's set-up)
+// are per-lane work inside the loop and K per-task arrays live in local memory — 17.9 ms (K = 8) and 20.8 ms (K = 4) against
+// 13.4 ms for gq_sample_digits, with more executed instructions (10.2 G vs 9.2 G) at a lower issue rate.
 struct BatchLane {
     ChaChaStream g;
     KarneyMachine km;
@@ -462,6 +497,8 @@ GP_HD void gauss_integers_batch(const Seed256 &seed, double sigma, uint64_t glob
 #pragma unroll
         for (int i = 0; i < 8; i++) key[i] = s.key[i];
     }
+    KarneyScale sc;
+    sc.init(sigma);
     BatchLane ln;
     ln.start();
     for (;;) {
@@ -474,59 +511,13 @@ GP_HD void gauss_integers_batch(const Seed256 &seed, double sigma, uint64_t glob
             } else {
                 if (ln.cur >= (uint32_t)K || !ln.at_boundary()) break;
                 ln.resume(key, global_poly + 1, coeff0 + (uint64_t)ln.cur * stride + 1, 0);
-                ln.km.begin(0.0, sigma);
+                ln.km.begin(0.0, sc);
             }
         }
         if (!ln.active && ln.cur >= (uint32_t)K) break;
         const uint64_t w = ln.g.next();
         if (ln.active) ln.km.step(w);  // else: waiting for the boundary, the word is dropped
     }
-}
-
-// K G-lattice tasks of one (poly, tower): coefficients coeff0 + k * stride, source residues values[k]; digits_out[k * DMAX + i]
-template <int DMAX, int K>
-GP_HD void gq_sample_digits_batch(const Seed256 &seed, const uint64_t *values, uint64_t q, uint32_t base_bits, uint32_t dpt, double c,
-                                  uint32_t tower, uint64_t poly, uint64_t coeff0, uint64_t stride, int64_t *digits_out) {
-    GqTower<DMAX> tw;
-    tw.init(q, base_bits, dpt, c);
-    uint32_t keys[K][8];
-    double a[K][DMAX];
-    int64_t z[K][DMAX];
-    for (int k = 0; k < K; k++) {  // up front, all lanes active: sub-key, continuous normals, target
-        ChaChaStream s;
-        s.open(seed, (uint64_t)tower + 1, poly + 1, coeff0 + (uint64_t)k * stride + 1, kDomGadget);
-#pragma unroll
-        for (int i = 0; i < 8; i++) keys[k][i] = s.key[i];
-        tw.target(s, values[k], a[k]);
-    }
-    const uint32_t used = 2 * dpt;  // words behind the dpt normals (ChaChaStream::normal takes two)
-    BatchLane ln;
-    ln.start();
-    for (;;) {
-        for (;;) {  // word-free transitions, as in gauss_integers_batch; a finished draw may also start the task's next draw
-            if (ln.active) {
-                if (!ln.km.done()) break;
-                double mean, sd;
-                if (tw.chain(ln.drawn, ln.km.result, a[ln.cur], z[ln.cur], mean, sd)) {
-                    ln.km.begin(mean, sd);
-                    ++ln.drawn;
-                } else {
-                    ++ln.cur, ln.active = false;
-                }
-            } else {
-                if (ln.cur >= (uint32_t)K || !ln.at_boundary()) break;
-                ln.resume(keys[ln.cur], (uint64_t)tower + 1, poly + 1, used);
-                ln.km.begin(-a[ln.cur][tw.last] / tw.cv[tw.last], tw.sigma / tw.cv[tw.last]);
-            }
-        }
-        if (!ln.active && ln.cur >= (uint32_t)K) break;
-        const uint64_t w = ln.g.next();
-        if (ln.active) {
-            if (ln.skip) --ln.skip;  // a word the up-front phase has used
-            else ln.km.step(w);
-        }
-    }
-    for (int k = 0; k < K; k++) tw.digits(values[k], z[k], digits_out + (size_t)k * DMAX);
 }
 
 // ---- perturbation p1: per-coefficient 2d x 2d conditional Gaussian ----------------------
@@ -680,9 +671,9 @@ __global__ void __launch_bounds__(128) gauss_samp_gq_kernel(const T *__restrict_
     }
 }
 
-// ---- lane-balanced kernels: a warp owns 32 K consecutive coefficients of one polynomial (n % (32 K) == 0); lane l runs
-// coefficients c0 + l + 32 k through gauss_integers_batch / gq_sample_digits_batch, so for every k the warp reads and
-// writes 32 consecutive words.  The bodies are GP_HD so the host harness walks the same index arithmetic.
+// ---- lane-balanced Gaussian kernel: a warp owns 32 K consecutive coefficients of one polynomial (n % (32 K) == 0); lane l
+// runs coefficients c0 + l + 32 k through gauss_integers_batch, so for every k the warp writes 32 consecutive words.  The body
+// is GP_HD so the host harness walks the same index arithmetic.
 template <typename T, int K>
 GP_HD void sample_gauss_batch_thread(size_t tid, T *__restrict__ dst, const SampleGeom &g, double sigma, const Seed256 &seed,
                                      const LimbConst<T> *__restrict__ lc) {
@@ -698,42 +689,10 @@ GP_HD void sample_gauss_batch_thread(size_t tid, T *__restrict__ dst, const Samp
     }
 }
 template <typename T, int K>
-GP_HD void gauss_samp_gq_batch_thread(size_t tid, const T *__restrict__ src, T *__restrict__ out, size_t src_polys, size_t src_cols,
-                                      uint32_t n, uint32_t limbs, uint32_t base_bits, uint32_t dpt, double c, const Seed256 &seed,
-                                      const LimbConst<T> *__restrict__ lc) {
-    constexpr int DMAX = 8;
-    const size_t base = (tid >> 5) * (size_t)(32 * K);
-    if (base >= src_polys * limbs * n) return;
-    const size_t pl = base / n, c0 = base - pl * n + (tid & 31);
-    const size_t poly = pl / limbs;
-    const uint32_t tower = (uint32_t)(pl - poly * limbs);
-    uint64_t values[K];
-    for (int k = 0; k < K; k++) values[k] = (uint64_t)src[pl * n + c0 + 32 * (size_t)k];
-    int64_t digits[K * DMAX];
-    gq_sample_digits_batch<DMAX, K>(seed, values, (uint64_t)lc[tower].q, base_bits, dpt, c, tower, poly, c0, 32, digits);
-    const size_t row = poly / src_cols, col = poly - row * src_cols;
-    const size_t ell = (size_t)dpt * limbs;
-    for (int k = 0; k < K; k++)
-        for (uint32_t dg = 0; dg < dpt; dg++) {
-            const size_t out_poly = (row * ell + (size_t)tower * dpt + dg) * src_cols + col;
-            T *p = out + out_poly * limbs * (size_t)n + c0 + 32 * (size_t)k;
-            for (uint32_t l = 0; l < limbs; l++) p[(size_t)l * n] = small_to_residue<T>(digits[k * DMAX + dg], lc[l]);
-        }
-}
-template <typename T, int K>
 __global__ void __launch_bounds__(128) sample_gauss_batch_kernel(T *__restrict__ dst, SampleGeom g, double sigma, Seed256 seed,
                                                                  const LimbConst<T> *__restrict__ lc) {
     sample_gauss_batch_thread<T, K>((size_t)blockIdx.x * blockDim.x + threadIdx.x, dst, g, sigma, seed, lc);
 }
-template <typename T, int K>
-__global__ void __launch_bounds__(128) gauss_samp_gq_batch_kernel(const T *__restrict__ src, T *__restrict__ out, size_t src_polys,
-                                                                  size_t src_cols, uint32_t n, uint32_t limbs, uint32_t base_bits,
-                                                                  uint32_t dpt, double c, Seed256 seed,
-                                                                  const LimbConst<T> *__restrict__ lc) {
-    gauss_samp_gq_batch_thread<T, K>((size_t)blockIdx.x * blockDim.x + threadIdx.x, src, out, src_polys, src_cols, n, limbs, base_bits,
-                                     dpt, c, seed, lc);
-}
-
 // covariance factorisation: one thread per coefficient (limb 0 of A, B, D in coefficient form)
 template <typename T>
 __global__ void __launch_bounds__(128) p1_factor_kernel(const T *__restrict__ a, const T *__restrict__ b, const T *__restrict__ dm,

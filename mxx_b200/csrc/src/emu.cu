@@ -538,23 +538,6 @@ int do_sample_gauss_batched(int logn, uint32_t limbs, const uint64_t *moduli, do
     for (size_t i = 0; i < dst.size(); i++) out[i] = (uint64_t)dst[i];
     return 0;
 }
-template <typename T, int K>
-int do_gauss_samp_batched(int logn, uint32_t limbs, const uint64_t *moduli, const uint64_t *src, size_t rows, size_t cols,
-                          uint32_t base_bits, uint32_t dpt, double c, const uint64_t *seed, uint64_t *out) {
-    Emu<T> e(logn, limbs, moduli);
-    const uint32_t n = 1u << logn;
-    if (n % (32 * K) || dpt > 8) return 1;
-    Seed256 sd;
-    for (int i = 0; i < 4; i++) sd.w[i] = seed[i];
-    const size_t polys = rows * cols;
-    std::vector<T> s(polys * limbs * n), dst(polys * dpt * limbs * limbs * n);
-    for (size_t i = 0; i < s.size(); i++) s[i] = (T)src[i];
-    const size_t threads = polys * limbs * n / K;
-    for (size_t tid = 0; tid < threads; tid++)
-        gauss_samp_gq_batch_thread<T, K>(tid, s.data(), dst.data(), polys, cols, n, limbs, base_bits, dpt, c, sd, e.tab.limb.data());
-    for (size_t i = 0; i < dst.size(); i++) out[i] = (uint64_t)dst[i];
-    return 0;
-}
 }  // namespace
 
 extern "C" {
@@ -597,17 +580,6 @@ int emu_sample_gauss_batched(int batch, int force_wide, int logn, uint32_t limbs
 #undef EMU_CALL
     }
 #define EMU_CALL(K) do_sample_gauss_batched<uint32_t, K>(logn, limbs, moduli, sigma, seed, rows, local_cols, full_cols, col_offset, out)
-    EMU_BATCH_SWITCH(EMU_CALL)
-#undef EMU_CALL
-}
-int emu_gauss_samp_batched(int batch, int force_wide, int logn, uint32_t limbs, const uint64_t *moduli, const uint64_t *src, size_t rows,
-                           size_t cols, uint32_t base_bits, uint32_t dpt, double c, const uint64_t *seed, uint64_t *out) {
-    if (force_wide || wide_for(moduli, limbs)) {
-#define EMU_CALL(K) do_gauss_samp_batched<uint64_t, K>(logn, limbs, moduli, src, rows, cols, base_bits, dpt, c, seed, out)
-        EMU_BATCH_SWITCH(EMU_CALL)
-#undef EMU_CALL
-    }
-#define EMU_CALL(K) do_gauss_samp_batched<uint32_t, K>(logn, limbs, moduli, src, rows, cols, base_bits, dpt, c, seed, out)
     EMU_BATCH_SWITCH(EMU_CALL)
 #undef EMU_CALL
 }

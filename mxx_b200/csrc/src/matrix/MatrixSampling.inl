@@ -26,16 +26,18 @@ inline gp::Seed256 to_seed(const GpuRngSeed &s) {
 
 inline unsigned blocks_for(size_t items, unsigned threads) { return (unsigned)((items + threads - 1) / threads); }
 
-// Tasks per lane of the lane-balanced Gaussian kernels (sampling.cuh gauss_integers_batch / gq_sample_digits_batch):
-// MXX_SAMPLER_BATCH = 1 (one task per thread, the round-1 kernels), 2, 4 or 8.  A warp owns 32 K consecutive
+// Tasks per lane of the lane-balanced Gaussian kernel (sampling.cuh gauss_integers_batch): MXX_SAMPLER_BATCH = 1 (one task per
+// thread), 2, 4 or 8 (default, 12.2 -> 8.7 ms on the C5 matrix, profiles/r02_sampler_lab.txt).  A warp owns 32 K consecutive
 // coefficients of one polynomial, so K is halved until 32 K divides the ring dimension.
-inline int sampler_batch(uint32_t n) {
-    static const int knob = getenv("MXX_SAMPLER_BATCH") ? atoi(getenv("MXX_SAMPLER_BATCH")) : 4;
+inline int batch_for(int knob, uint32_t n) {
     int k = knob >= 8 ? 8 : (knob >= 4 ? 4 : (knob >= 2 ? 2 : 1));
     while (k > 1 && n % (32u * (unsigned)k)) k >>= 1;
     return k;
 }
-
+inline int sampler_batch(uint32_t n) {
+    static const int knob = getenv("MXX_SAMPLER_BATCH") ? atoi(getenv("MXX_SAMPLER_BATCH")) : 8;
+    return batch_for(knob, n);
+}
 template <typename T>
 int run_sample_distribution(GpuContext *ctx, GpuMatrix *out, int dist, double sigma, const gp::Seed256 &seed, size_t full_cols,
                             size_t col_offset) {
@@ -102,21 +104,7 @@ int run_gauss_samp(GpuContext *ctx, const GpuMatrix *src, GpuMatrix *out, uint32
     if (items > (size_t)0x7fffffff * 128) return gp::set_error("matrix too large in gpu_matrix_gauss_samp_gq_arb_base");
     const auto *lc = (const gp::LimbConst<T> *)ctx->d_limb;
     const unsigned grid = blocks_for(items, 128);
-    const int batch = dpt <= 8 ? sampler_batch(n) : 1;
-    if (batch > 1) {
-        switch (batch) {
-#define GP_GQB(K)                                                                                                              \
-    case K:                                                                                                                    \
-        gp::gauss_samp_gq_batch_kernel<T, K><<<blocks_for(items / K, 128), 128, 0, gp::cur(ctx)>>>(                            \
-            (const T *)src->data, (T *)out->data, src->polys(), src->cols, n, limbs, base_bits, dpt, c, seed, lc);             \
-        break;
-            GP_GQB(2)
-            GP_GQB(4)
-            default:
-                GP_GQB(8)
-#undef GP_GQB
-        }
-    } else if (dpt <= 8)
+    if (dpt <= 8)
         gp::gauss_samp_gq_kernel<T, 8><<<grid, 128, 0, gp::cur(ctx)>>>((const T *)src->data, (T *)out->data, src->polys(), src->cols,
                                                                        n, limbs, base_bits, dpt, c, seed, lc);
     else
