@@ -432,7 +432,10 @@ int do_matmul(int logn, uint32_t limbs, const uint64_t *moduli, uint64_t *out, c
     switch (variant) {
         case 0: matmul_grid<T, VMAX, 1, 4>(o, a, b, g, e.tab.limb.data()); break;
         case 1: matmul_grid<T, VMAX, 2, 4>(o, a, b, g, e.tab.limb.data()); break;
-        case 2: matmul_grid<T, VMAX / 2, 4, 4>(o, a, b, g, e.tab.limb.data()); break;
+        case 2:  // the four-row tiles of run_matmul: 4 x 2 full vectors for 32-bit words, 4 x 4 half vectors for 64-bit words
+            if constexpr (sizeof(T) == 4) matmul_grid<T, VMAX, 4, 2>(o, a, b, g, e.tab.limb.data());
+            else matmul_grid<T, VMAX / 2, 4, 4>(o, a, b, g, e.tab.limb.data());
+            break;
         default: matmul_grid<T, 1, 1, 1>(o, a, b, g, e.tab.limb.data()); break;
     }
     widen(o, out);
