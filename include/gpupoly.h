@@ -145,6 +145,14 @@ int gpu_matrix_intt_to(GpuMatrix *dst, size_t dst_row, const GpuMatrix *src);
  * (src/bgg/encoding.rs:135) applied in place to the vector rows of a stacked product, one launch. */
 int gpu_matrix_add_scaled_block(GpuMatrix *out, const GpuMatrix *src, const GpuMatrix *scalar, size_t dst_row, size_t dst_col,
                                 size_t src_row, size_t src_col, size_t rows, size_t cols);
+/* gpu_matrix_decompose_base for callers that must not allocate (CUDA graph capture, serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.  Same arguments, validation
+ * and result as gpu_matrix_decompose_base; the coefficient form of an EVAL input goes to a static device array of
+ * GPU_NOALLOC_SCRATCH_BYTES instead of pool memory, and an EVAL input larger than that is rejected with an error.  The call
+ * makes no cudaMalloc / cudaFree / cudaMallocAsync.  All calls on a device share the array: calls whose kernels overlap on
+ * the GPU (two contexts or streams on one device) race on it; calls on one context are stream-ordered. */
+#define GPU_NOALLOC_SCRATCH_BYTES (16u << 20)
+int gpu_matrix_decompose_base_noalloc(const GpuMatrix *src, uint32_t base_bits, GpuMatrix *out);
 /* Big-integer coefficients <-> residues ON THE DEVICE: the conversion step either side of the path
  * (SURVEY 8f-4).  words[(poly * n + j) * words_per_coeff + w], little-endian u64 words of the coefficient.
  * load: every active limb receives the coefficient mod q_limb — the host BigUint `%` loop of

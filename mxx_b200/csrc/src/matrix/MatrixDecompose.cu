@@ -5,3 +5,4 @@
 #include "MatrixCommon.inl"
 #include "MatrixNttPlan.inl"
 #include "MatrixDecompose.inl"
+#include "MatrixNoAlloc.inl"

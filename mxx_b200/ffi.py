@@ -78,6 +78,7 @@ EXTENSIONS = {
     "gpu_matrix_mul_decompose_gathered": (C.c_int, [H, H, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, u64p, C.c_size_t, C.c_size_t,
                                                    C.c_size_t, C.c_size_t, C.c_uint32, C.c_int]),
     "gpu_matrix_intt_to": (C.c_int, [H, C.c_size_t, H]),
+    "gpu_matrix_decompose_base_noalloc": (C.c_int, [H, C.c_uint32, H]),
     "gpu_matrix_add_scaled_block": (C.c_int, [H, H, H] + [C.c_size_t] * 6),
     "gpu_matrix_load_bigint_batch": (C.c_int, [H, u64p, C.c_size_t, C.c_int, vpp]),
     "gpu_matrix_store_bigint_batch": (C.c_int, [H, u64p, C.c_size_t, vpp]),

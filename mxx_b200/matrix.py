@@ -500,6 +500,16 @@ class GpuDCRTPolyMatrix:
         check_status(fn(self.raw, p.base_bits, out.raw), "gpu_matrix_decompose_base", self._L)
         return out
 
+    def decompose_noalloc(self, out=None):
+        """gpu_matrix_decompose_base_noalloc (no counterpart in the reference): the same decomposition with the scratch in a
+        static device array; `out` may be a matrix created earlier so that the call itself allocates nothing at all."""
+        p = self.params
+        ell = p.digits_per_tower * (self.level + 1)
+        if out is None:
+            out = GpuDCRTPolyMatrix(p, self.nrow * ell, self.ncol, self.level, True)
+        check_status(self._L.gpu_matrix_decompose_base_noalloc(self.raw, p.base_bits, out.raw), "gpu_matrix_decompose_base_noalloc", self._L)
+        return out
+
     def decompose(self):  # gpu_dcrt_poly.rs:1276-1284
         return self._decompose(False)
 
