@@ -279,12 +279,21 @@ GP_HD void matmul_thread(uint32_t bx, uint32_t by, uint32_t bz, uint32_t tid, ui
 // CTAs resident at one time share a few (limb, slot chunk) slices of A and every A word is fetched from HBM once.
 // With the slot chunks fastest, one sweep over x touches ALL of A before any of it is used again: a left operand
 // larger than the L2 (C3-b: 4 x 120 polynomials = 472 MB) is streamed once per column tile.
-// MINB > 1 caps the registers of the wide tiles: the 4 x 2 tile at V = 4 takes 254 registers uncapped (one CTA of 128 threads
-// per SM quarter, every warp waiting on its loads); capped at 168 (three CTAs) it is 26 % faster (tools/matmul_rows_lab.cu).
-template <typename T, int V, int TR, int TC, int UNROLL = 2, int NT = 128, bool COLS_FAST = false, int MINB = 1>
-__global__ void __launch_bounds__(NT, MINB)
+template <typename T, int V, int TR, int TC, int UNROLL = 2, int NT = 128, bool COLS_FAST = false>
+__global__ void __launch_bounds__(NT)
 matmul_kernel(T *__restrict__ out, const T *__restrict__ A, const T *__restrict__ B, MatmulGeom g,
               const LimbConst<T> *__restrict__ lc) {
+    matmul_thread<T, V, TR, TC, UNROLL>(COLS_FAST ? blockIdx.y : blockIdx.x, COLS_FAST ? blockIdx.x : blockIdx.y, blockIdx.z,
+                                        threadIdx.x, blockDim.x, out, A, B, g, lc);
+}
+// The same with the registers capped through a minimum number of resident CTAs: the 4 x 2 tile at V = 4 takes 254 registers
+// uncapped (every warp waiting on its own loads at 18 % occupancy); capped at 168 (three CTAs of 128 threads) it is 26 %
+// faster (tools/matmul_rows_lab.cu).  A kernel of its own: `__launch_bounds__(NT, 1)` is NOT the same as `__launch_bounds__(NT)`
+// to ptxas — it took the one-row C1-R tile from 164 to 214 registers and from 0.545 to 0.625 ms.
+template <typename T, int V, int TR, int TC, int UNROLL, int NT, bool COLS_FAST, int MINB>
+__global__ void __launch_bounds__(NT, MINB)
+matmul_capped_kernel(T *__restrict__ out, const T *__restrict__ A, const T *__restrict__ B, MatmulGeom g,
+                     const LimbConst<T> *__restrict__ lc) {
     matmul_thread<T, V, TR, TC, UNROLL>(COLS_FAST ? blockIdx.y : blockIdx.x, COLS_FAST ? blockIdx.x : blockIdx.y, blockIdx.z,
                                         threadIdx.x, blockDim.x, out, A, B, g, lc);
 }

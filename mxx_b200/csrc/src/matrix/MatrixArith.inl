@@ -54,10 +54,15 @@ int launch_matmul_tile(GpuContext *ctx, T *out, const T *A, const T *B, const gp
     return for_each_matmul_slab(g, TR, TC, (size_t)g.limbs << g.logn, [&](const gp::MatmulGeom &s, size_t a_off, size_t o_off) {
         const unsigned slot_ctas = s.limbs * per_limb, col_tiles = (s.cols + TC - 1) / TC, row_tiles = (s.rows + TR - 1) / TR;
         const auto *lc = (const gp::LimbConst<T> *)ctx->d_limb;
-        if (TR >= 2 && col_tiles > 1 && matmul_cols_fast(slot_ctas))
-            gp::matmul_kernel<T, V, TR, TC, UNROLL, NT, true, MINB><<<dim3(col_tiles, slot_ctas, row_tiles), threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, lc);
-        else
-            gp::matmul_kernel<T, V, TR, TC, UNROLL, NT, false, MINB><<<dim3(slot_ctas, col_tiles, row_tiles), threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, lc);
+        const bool cols_fast = TR >= 2 && col_tiles > 1 && matmul_cols_fast(slot_ctas);
+        const dim3 grid = cols_fast ? dim3(col_tiles, slot_ctas, row_tiles) : dim3(slot_ctas, col_tiles, row_tiles);
+        if constexpr (MINB > 1) {
+            if (cols_fast) gp::matmul_capped_kernel<T, V, TR, TC, UNROLL, NT, true, MINB><<<grid, threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, lc);
+            else gp::matmul_capped_kernel<T, V, TR, TC, UNROLL, NT, false, MINB><<<grid, threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, lc);
+        } else {
+            if (cols_fast) gp::matmul_kernel<T, V, TR, TC, UNROLL, NT, true><<<grid, threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, lc);
+            else gp::matmul_kernel<T, V, TR, TC, UNROLL, NT, false><<<grid, threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, lc);
+        }
         gp::count_launch();
         GP_CHECK_LAUNCH("matmul_kernel");
         return 0;
