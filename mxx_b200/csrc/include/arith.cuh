@@ -286,17 +286,8 @@ matmul_kernel(T *__restrict__ out, const T *__restrict__ A, const T *__restrict_
     matmul_thread<T, V, TR, TC, UNROLL>(COLS_FAST ? blockIdx.y : blockIdx.x, COLS_FAST ? blockIdx.x : blockIdx.y, blockIdx.z,
                                         threadIdx.x, blockDim.x, out, A, B, g, lc);
 }
-// The same with the registers capped through a minimum number of resident CTAs: the 4 x 2 tile at V = 4 takes 254 registers
-// uncapped (every warp waiting on its own loads at 18 % occupancy); capped at 168 (three CTAs of 128 threads) it is 26 %
-// faster (tools/matmul_rows_lab.cu).  A kernel of its own: `__launch_bounds__(NT, 1)` is NOT the same as `__launch_bounds__(NT)`
-// to ptxas — it took the one-row C1-R tile from 164 to 214 registers and from 0.545 to 0.625 ms.
-template <typename T, int V, int TR, int TC, int UNROLL, int NT, bool COLS_FAST, int MINB>
-__global__ void __launch_bounds__(NT, MINB)
-matmul_capped_kernel(T *__restrict__ out, const T *__restrict__ A, const T *__restrict__ B, MatmulGeom g,
-                     const LimbConst<T> *__restrict__ lc) {
-    matmul_thread<T, V, TR, TC, UNROLL>(COLS_FAST ? blockIdx.y : blockIdx.x, COLS_FAST ? blockIdx.x : blockIdx.y, blockIdx.z,
-                                        threadIdx.x, blockDim.x, out, A, B, g, lc);
-}
+// Launch bounds: `__launch_bounds__(NT)` alone.  `__launch_bounds__(NT, 1)` is NOT the same to ptxas: it took the one-row C1-R
+// tile from 164 to 214 registers (0.545 -> 0.625 ms) and the wide tiles from 162-168 to 254 (profiles/r02_matmul_rows_lab.txt).
 
 // ---- the same product on the FP64 pipe (u64 words, every modulus below 2^51; modarith.cuh f64_*) --------------
 // A 64-bit lazy MAC is a 128-bit multiply-add (measured 0.78e12 MAC/s); on exact doubles a term costs 7 FP64

@@ -47,22 +47,17 @@ bool matmul_cols_fast(unsigned slot_ctas) {
     return knob != 0 && slot_ctas <= kMaxGridYZ;
 }
 
-template <typename T, int V, int TR, int TC, int UNROLL = 2, int NT = 128, int MINB = 1>
+template <typename T, int V, int TR, int TC, int UNROLL = 2, int NT = 128>
 int launch_matmul_tile(GpuContext *ctx, T *out, const T *A, const T *B, const gp::MatmulGeom &g) {
     const unsigned threads = NT;
     const unsigned per_limb = (unsigned)(((size_t)ctx->N / V + threads - 1) / threads);
     return for_each_matmul_slab(g, TR, TC, (size_t)g.limbs << g.logn, [&](const gp::MatmulGeom &s, size_t a_off, size_t o_off) {
         const unsigned slot_ctas = s.limbs * per_limb, col_tiles = (s.cols + TC - 1) / TC, row_tiles = (s.rows + TR - 1) / TR;
         const auto *lc = (const gp::LimbConst<T> *)ctx->d_limb;
-        const bool cols_fast = TR >= 2 && col_tiles > 1 && matmul_cols_fast(slot_ctas);
-        const dim3 grid = cols_fast ? dim3(col_tiles, slot_ctas, row_tiles) : dim3(slot_ctas, col_tiles, row_tiles);
-        if constexpr (MINB > 1) {
-            if (cols_fast) gp::matmul_capped_kernel<T, V, TR, TC, UNROLL, NT, true, MINB><<<grid, threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, lc);
-            else gp::matmul_capped_kernel<T, V, TR, TC, UNROLL, NT, false, MINB><<<grid, threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, lc);
-        } else {
-            if (cols_fast) gp::matmul_kernel<T, V, TR, TC, UNROLL, NT, true><<<grid, threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, lc);
-            else gp::matmul_kernel<T, V, TR, TC, UNROLL, NT, false><<<grid, threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, lc);
-        }
+        if (TR >= 2 && col_tiles > 1 && matmul_cols_fast(slot_ctas))
+            gp::matmul_kernel<T, V, TR, TC, UNROLL, NT, true><<<dim3(col_tiles, slot_ctas, row_tiles), threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, lc);
+        else
+            gp::matmul_kernel<T, V, TR, TC, UNROLL, NT, false><<<dim3(slot_ctas, col_tiles, row_tiles), threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, lc);
         gp::count_launch();
         GP_CHECK_LAUNCH("matmul_kernel");
         return 0;
@@ -114,12 +109,11 @@ template <typename T> int gpm::run_matmul(GpuContext *ctx, T *out, const T *A, c
     }
     // Register tile: the wider the tile the fewer operand loads per product.  rows == 1 (the
     // BGG / bench_matrix_mul shape) streams B once and re-reads A from L2.
-    // four rows: for 32-bit words a 4 x 2 tile of full 128-bit vectors with the registers capped at 168 (three CTAs per SM)
-    // — 0.775 ms against 1.047 ms for the 4 x 4 tile of half vectors on one column chunk of C3-b (tools/matmul_rows_lab.cu,
-    // profiles/r02_matmul_rows_lab.txt; the uncapped tiles take 254 registers and run at 18 % occupancy waiting on loads)
+    // four rows: for 32-bit words a 4 x 2 tile of full 128-bit vectors (162 registers) — 0.77 ms against 1.75 ms for the 4 x 4
+    // tile of half vectors on one column chunk of C3-b (tools/matmul_rows_lab.cu, profiles/r02_matmul_rows_lab.txt)
     if constexpr (sizeof(T) == 4) {
         static const bool wide_rows = !(getenv("MXX_MATMUL_ROWS4") && getenv("MXX_MATMUL_ROWS4")[0] == '0');
-        if (g.rows >= 4 && wide_rows) return launch_matmul_tile<T, VMAX, 4, 2, 2, 128, 3>(ctx, out, A, B, g);
+        if (g.rows >= 4 && wide_rows) return launch_matmul_tile<T, VMAX, 4, 2>(ctx, out, A, B, g);
     }
     if (g.rows >= 4) return launch_matmul_tile<T, VMAX / 2, 4, 4>(ctx, out, A, B, g);
     if (g.rows >= 2) return launch_matmul_tile<T, VMAX, 2, 4>(ctx, out, A, B, g);

@@ -30,10 +30,35 @@ using namespace gp;
 #ifndef LAB_MINB
 #define LAB_MINB 1
 #endif
+#ifndef LAB_R
+#define LAB_R 4
+#endif
+#ifndef LAB_K
+#define LAB_K 120
+#endif
+#ifndef LAB_C
+#define LAB_C 18
+#endif
+#ifndef LAB_LIMBS
+#define LAB_LIMBS 15
+#endif
+#ifndef LAB_LOGN
+#define LAB_LOGN 14
+#endif
+#ifndef LAB_QBITS
+#define LAB_QBITS 24
+#endif
 typedef uint32_t T;
 
+// LAB_MINB = 0: __launch_bounds__(threads) alone, as the uncapped library kernels are declared (NOT the same register
+// allocation as a minimum of 1: ptxas takes 162-166 registers for the wide tiles then, 254 with (threads, 1))
+#if LAB_MINB == 0
+#define LAB_BOUNDS __launch_bounds__(LAB_SL * LAB_CG)
+#else
+#define LAB_BOUNDS __launch_bounds__(LAB_SL * LAB_CG, LAB_MINB)
+#endif
 template <typename T, int V, int TR, int TC, int UNROLL, int SL, int CG>
-__global__ void __launch_bounds__(SL * CG, LAB_MINB)
+__global__ void LAB_BOUNDS
 matmul_cg_kernel(T *__restrict__ out, const T *__restrict__ A, const T *__restrict__ B, MatmulGeom g, const LimbConst<T> *__restrict__ lc) {
     const uint32_t sx = threadIdx.x % SL, cg = threadIdx.x / SL;
     const uint32_t by = blockIdx.x * CG + cg;
@@ -49,15 +74,16 @@ __global__ void fill_kernel(T *p, size_t nwords, T q, uint32_t salt) {
 }
 
 int main() {
-    const uint32_t logn = 14, n = 1u << logn, limbs = 15, r = 4, k = 120, c = 18;
-    const uint64_t q = 16515073ull;
+    // default: a C3-b column chunk; -DLAB_R=2 -DLAB_K=32 -DLAB_C=32 -DLAB_LIMBS=16 -DLAB_LOGN=15 -DLAB_QBITS=28: the product of a C4 28-bit gate
+    const uint32_t logn = LAB_LOGN, n = 1u << logn, limbs = LAB_LIMBS, r = LAB_R, k = LAB_K, c = LAB_C;
+    const uint64_t q = LAB_QBITS == 24 ? 16515073ull : 268369921ull;
     std::vector<LimbConst<T>> lc(limbs);
     for (auto &x : lc) {
         x = LimbConst<T>{};
         x.q = (T)q; x.q2 = (T)(2 * q);
         x.mu64 = (uint64_t)((((unsigned __int128)1) << 64) / q);
         x.one_s = (T)((((unsigned __int128)1) << 32) / q);
-        x.bits = 24;
+        x.bits = LAB_QBITS;
     }
     const size_t pw = (size_t)limbs << logn;
     T *A, *B, *O, *O2; LimbConst<T> *L;
@@ -68,7 +94,7 @@ int main() {
     fill_kernel<<<1184, 256>>>(A, (size_t)r * k * pw, (T)q, 2);
     cudaMemcpy(L, lc.data(), limbs * sizeof(LimbConst<T>), cudaMemcpyHostToDevice);
     MatmulGeom g{}; g.rows = r; g.inner = k; g.cols = c; g.b_cols = c; g.b_col0 = 0; g.out_cols = c; g.out_col0 = 0;
-    g.limbs = limbs; g.logn = logn; g.fold = 65536;
+    g.limbs = limbs; g.logn = logn; g.fold = LAB_QBITS == 24 ? 65536 : 128;
     {   // comparison result: the 4 x 4 tile of half vectors, column tiles fastest
         const unsigned per_limb = (n / 2 + 127) / 128;
         matmul_kernel<T, 2, 4, 4, 2, 128, true><<<dim3((c + 3) / 4, limbs * per_limb, (r + 3) / 4), 128>>>(O2, A, B, g, L);
