@@ -64,7 +64,7 @@ int launch_matmul_tile(GpuContext *ctx, T *out, const T *A, const T *B, const gp
     });
 }
 
-template <int V, int TR, int TC, int UNROLL = 2, int NT = 128>
+template <int V, int TR, int TC, int UNROLL = 2, int NT = 128, int MINB = 512 / NT>
 int launch_matmul_f64_tile(GpuContext *ctx, uint64_t *out, const uint64_t *A, const uint64_t *B, const gp::MatmulGeom &g) {
     const unsigned threads = NT;
     const unsigned per_limb = (unsigned)(((size_t)ctx->N / V + threads - 1) / threads);
@@ -72,9 +72,9 @@ int launch_matmul_f64_tile(GpuContext *ctx, uint64_t *out, const uint64_t *A, co
         const unsigned slot_ctas = s.limbs * per_limb, col_tiles = (s.cols + TC - 1) / TC, row_tiles = (s.rows + TR - 1) / TR;
         const auto *lc = (const gp::LimbConst<gp::F64> *)ctx->d_limb_f64;
         if (TR >= 2 && col_tiles > 1 && matmul_cols_fast(slot_ctas))
-            gp::matmul_f64_kernel<V, TR, TC, UNROLL, NT, true><<<dim3(col_tiles, slot_ctas, row_tiles), threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, lc);
+            gp::matmul_f64_kernel<V, TR, TC, UNROLL, NT, true, MINB><<<dim3(col_tiles, slot_ctas, row_tiles), threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, lc);
         else
-            gp::matmul_f64_kernel<V, TR, TC, UNROLL, NT, false><<<dim3(slot_ctas, col_tiles, row_tiles), threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, lc);
+            gp::matmul_f64_kernel<V, TR, TC, UNROLL, NT, false, MINB><<<dim3(slot_ctas, col_tiles, row_tiles), threads, 0, gp::cur(ctx)>>>(out + o_off, A + a_off, B, s, lc);
         gp::count_launch();
         GP_CHECK_LAUNCH("matmul_f64_kernel");
         return 0;
@@ -102,7 +102,9 @@ template <typename T> int gpm::run_matmul(GpuContext *ctx, T *out, const T *A, c
         if (ctx->f64_ntt && ctx->f64_matmul) {  // moduli < 2^51: the product on the FP64 pipe (arith.cuh)
             g.fold = ctx->f64_mac_fold;
             if (g.rows >= 4) return launch_matmul_f64_tile<VMAX / 2, 4, 4, 1>(ctx, out, A, B, g);
-            if (g.rows >= 2) return launch_matmul_f64_tile<VMAX, 2, 4, 1>(ctx, out, A, B, g);
+            // two rows (the C4 gate): five resident CTAs (94 registers) — 0.265 ms against 0.294 ms at four (108 registers) and
+            // 0.357 ms at six on the gate's product (tools/matmul_f64_lab.cu, profiles/r02_matmul_rows_lab.txt)
+            if (g.rows >= 2) return launch_matmul_f64_tile<VMAX, 2, 4, 1, 128, 5>(ctx, out, A, B, g);
             if (g.cols % 6 == 0) return launch_matmul_f64_tile<VMAX, 1, 6, 2, 64>(ctx, out, A, B, g);
             return launch_matmul_f64_tile<VMAX, 1, 1, 6, 128>(ctx, out, A, B, g);
         }
